@@ -1,0 +1,200 @@
+/* relayrl_b200.h -- C ABI of librelayrl_b200.so: the B200-native (sm_100a) learner hot path of
+ * RelayRL (trajectory ingest -> reward-to-go/GAE scan -> advantage normalisation -> policy/value
+ * MLP forward/backward -> Adam -> parameter hand-off -> batched actor inference).
+ *
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns an int32 status
+ * (0 = RRL_OK, negative = RRL_E*), never throws, and never falls back to the CPU: without a
+ * CUDA device the calls fail with RRL_ECUDA.  Citations are to the reference tree
+ * (jrcalgo/RelayRL-prototype), paths relative to relayrl_framework/.
+ *
+ * Threading: calls on one handle must be serialised by the caller (the reference serialises
+ * every algorithm call behind one asyncio.Lock, src/native/python/python_algorithm_reply.py:66,77,100)
+ * but may come from different OS threads; every call selects the handle's device itself.
+ * Different handles are independent.
+ */
+#ifndef RELAYRL_B200_H
+#define RELAYRL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RRL_ABI_VERSION 1
+
+/* status codes */
+#define RRL_OK 0
+#define RRL_EINVAL (-1)     /* bad argument / unsupported shape */
+#define RRL_ECUDA (-2)      /* CUDA runtime error (see rrl_last_error) */
+#define RRL_ECAPACITY (-3)  /* replay buffer full: reference `assert self.ptr < self.max_size`
+                               (src/native/python/algorithms/REINFORCE/replay_buffer.py:38,87) */
+#define RRL_ESTATE (-4)     /* call order violated (e.g. train before finish) */
+#define RRL_ENCCL (-5)      /* NCCL unavailable or failed */
+#define RRL_EFORMAT (-6)    /* malformed wire bytes (safetensors / pickle) */
+
+/* element types of host payloads (wire dtypes, src/types/action.rs:92-101) */
+#define RRL_F32 0
+#define RRL_F64 1
+
+/* how `logp` is defined: the reference gathers the RAW masked logit
+ * (src/native/python/algorithms/REINFORCE/kernel.py:33-37); mode 1 is the textbook log-softmax. */
+#define RRL_LOGP_REFERENCE 0
+#define RRL_LOGP_LOG_SOFTMAX 1
+
+#define RRL_NCCL_ID_BYTES 128
+
+typedef struct rrl_learner rrl_learner_t;
+typedef struct rrl_actor rrl_actor_t;
+
+/* Constructor arguments of the reference algorithm class
+ * (REINFORCE.__init__, src/native/python/algorithms/REINFORCE/REINFORCE.py:17-62) plus the
+ * hyper-parameters it reads through ConfigLoader (src/sys_utils/config_loader.rs:148-159;
+ * floats are f32 in Rust and arrive as f32-rounded doubles, src/bindings/python/o3_config_loader.rs:76-84). */
+typedef struct rrl_config {
+    int32_t obs_dim;         /* d */
+    int32_t act_dim;         /* A (discrete actions) */
+    int32_t hidden;          /* H of the two hidden layers; reference hard-codes 128 (REINFORCE.py:46,49) */
+    int32_t with_baseline;   /* with_vf_baseline */
+    int32_t train_vf_iters;  /* value Adam steps per epoch (REINFORCE.py:111) */
+    int32_t logp_mode;       /* RRL_LOGP_* */
+    int32_t device;          /* CUDA ordinal */
+    int32_t rank;            /* data-parallel rank; 0 when nranks == 1 */
+    int32_t nranks;          /* 1 = single GPU */
+    int32_t reserved0;
+    int64_t capacity;        /* buf_size, transitions */
+    double gamma, lam;       /* replay_buffer.py:30 */
+    double pi_lr, vf_lr;     /* REINFORCE.py:47,50 */
+    double adam_beta1, adam_beta2, adam_eps; /* torch.optim.Adam defaults 0.9, 0.999, 1e-8 */
+    uint8_t nccl_id[RRL_NCCL_ID_BYTES]; /* from rrl_nccl_unique_id on rank 0, when nranks > 1 */
+} rrl_config_t;
+
+/* A run of actions as the reference's receive_trajectory sees them
+ * (REINFORCE.py:70-95): row i is a transition (done[i] == 0) or a terminal marker
+ * (done[i] != 0: nothing is stored, rew[i] becomes the path's last_val, REINFORCE.py:86).
+ * Host pointers, struct-of-arrays, row-major.  Rows of terminal markers are ignored in
+ * obs/act/mask/val/logp.  Wire dtypes: obs/mask F64 from Python agents, else F32. */
+typedef struct rrl_batch_view {
+    const void *obs;     /* [count, obs_dim], obs_dtype */
+    const float *act;    /* [count] action index stored as f32 (replay_buffer.py:21) */
+    const void *mask;    /* [count, act_dim], mask_dtype */
+    const float *rew;    /* [count] */
+    const float *val;    /* [count] data['v'];   may be NULL without baseline */
+    const float *logp;   /* [count] data['logp_a'] */
+    const uint8_t *done; /* [count] */
+    int64_t count;
+    int32_t obs_dtype, mask_dtype; /* RRL_F32 | RRL_F64 */
+} rrl_batch_view_t;
+
+/* What REINFORCE.train_model stores in its logger (REINFORCE.py:117-125) + buffer statistics. */
+typedef struct rrl_epoch_stats {
+    double loss_pi, delta_loss_pi, kl, entropy; /* delta_loss_pi is identically 0 */
+    double loss_v, delta_loss_v, loss_v_old;
+    double adv_mean, adv_std;                   /* statistics_scalar, BaseReplayBuffer.py:30-53 */
+    int64_t n_transitions, n_episodes;          /* global over all ranks */
+    /* device time of the stages of this call, CUDA events on the library stream, milliseconds */
+    float ms_scan, ms_policy, ms_value, ms_total;
+    int32_t kernel_launches;                    /* kernels launched by this call */
+    int32_t reserved;
+} rrl_epoch_stats_t;
+
+/* ---- library ------------------------------------------------------------------------- */
+int32_t rrl_abi_version(void);
+const char *rrl_status_string(int32_t status);
+/* Message of the last failure on this handle (owned by the handle), or of the last failed
+ * create when h == NULL (thread-local). */
+const char *rrl_last_error(const rrl_learner_t *h);
+int32_t rrl_device_count(int32_t *count);
+/* Pinned host memory for callers that want the ingest copy to be truly asynchronous. */
+int32_t rrl_host_alloc(void **ptr, size_t bytes);
+int32_t rrl_host_free(void *ptr);
+int32_t rrl_nccl_unique_id(uint8_t out[RRL_NCCL_ID_BYTES]);
+void rrl_config_defaults(rrl_config_t *cfg);
+
+/* ---- learner: replaces REINFORCE + ReplayBuffer ------------------------------------------ */
+/* REINFORCE.__init__ (REINFORCE.py:17-62).  Weights start at zero: call rrl_set_params. */
+int32_t rrl_learner_create(const rrl_config_t *cfg, rrl_learner_t **out);
+int32_t rrl_learner_destroy(rrl_learner_t *h);
+
+/* Flat parameters in torch.nn.Linear order W1,b1,W2,b2,W3,b3, W row-major [out,in]
+ * (kernel.py:15-21; BaseKernel.py:25-39).  which: 0 = policy.pi_network, 1 = baseline.v_network. */
+int32_t rrl_param_count(const rrl_learner_t *h, int32_t which, int64_t *n);
+int32_t rrl_set_params(rrl_learner_t *h, int32_t which, const float *flat, int64_t n);
+int32_t rrl_get_params(rrl_learner_t *h, int32_t which, float *flat, int64_t n);
+/* Adam moments + step count (torch.optim.Adam state: exp_avg, exp_avg_sq, step). */
+int32_t rrl_get_opt_state(rrl_learner_t *h, int32_t which, float *m, float *v, int64_t n, int64_t *step);
+int32_t rrl_set_opt_state(rrl_learner_t *h, int32_t which, const float *m, const float *v, int64_t n, int64_t step);
+
+/* receive_trajectory's per-action loop + ReplayBuffer.store (REINFORCE.py:70-87,
+ * replay_buffer.py:34-46): packs rows into pinned staging, copies asynchronously into the flat
+ * device buffers, records episode offsets (successive path_start_idx values) on the host. */
+int32_t rrl_ingest_packed(rrl_learner_t *h, const rrl_batch_view_t *batch);
+/* Same, with device-resident SoA f32 inputs already free of terminal markers: `offsets`
+ * (n_ep + 1 entries relative to this batch, offsets[0] == 0) and `last_vals` (n_ep) are host arrays. */
+int32_t rrl_ingest_device(rrl_learner_t *h, const float *obs, const float *act, const float *mask,
+                          const float *rew, const float *val, const float *logp, int64_t count,
+                          const int64_t *offsets, const float *last_vals, int64_t n_ep);
+/* Wire formats: one safetensors blob per tensor field
+ * (src/types/action.rs:196-218,287-418; src/sys_utils/grpc_utils.rs:31-66 for the proto fields). */
+int32_t rrl_ingest_wire_action(rrl_learner_t *h, const uint8_t *obs_blob, size_t obs_len,
+                               const uint8_t *act_blob, size_t act_len, const uint8_t *mask_blob,
+                               size_t mask_len, float rew, const uint8_t *v_blob, size_t v_len,
+                               const uint8_t *logp_blob, size_t logp_len, uint8_t done);
+
+/* ReplayBuffer.finish_path for every closed path of the epoch (replay_buffer.py:48-79) and
+ * statistics_scalar over [0, ptr) (BaseReplayBuffer.py:30-53): one fused segmented reverse scan.
+ * Returns this rank's counts. */
+int32_t rrl_finish(rrl_learner_t *h, int64_t *n_transitions, int64_t *n_episodes);
+
+/* Parity taps (host outputs).  Offsets are the successive path_start_idx values, offsets[0] = 0. */
+int32_t rrl_get_offsets(rrl_learner_t *h, int64_t *out, int64_t cap, int64_t *n_written);
+int32_t rrl_get_returns(rrl_learner_t *h, float *out, int64_t cap);
+/* normalised != 0: (adv - mean) / std as ReplayBuffer.get returns it (replay_buffer.py:94-105). */
+int32_t rrl_get_advantages(rrl_learner_t *h, float *out, int64_t cap, int32_t normalised);
+int32_t rrl_get_adv_stats(rrl_learner_t *h, float *mean, float *std);
+
+/* REINFORCE.train_model (REINFORCE.py:97-125): ReplayBuffer.get() semantics (pointers reset),
+ * one policy Adam step, train_vf_iters value Adam steps.  Calls rrl_finish if it was not called. */
+int32_t rrl_train_epoch(rrl_learner_t *h, rrl_epoch_stats_t *stats);
+/* Pieces of the above for parity tests: losses and flat gradients at the current parameters on
+ * the current (finished) buffer; no update. which: 0 policy (out3 = loss_pi, kl, entropy), 1 value (loss_v). */
+int32_t rrl_eval_grad(rrl_learner_t *h, int32_t which, float *grad, int64_t n, double out3[3]);
+int32_t rrl_reset_buffer(rrl_learner_t *h);
+
+/* ---- actor: replaces PolicyWith[out]Baseline.step (kernel.py:99-107,128-135) as called from
+ * RelayRLAgent*::request_for_action (src/network/client/agent_zmq.rs:458-571) ----------------- */
+int32_t rrl_actor_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32_t with_baseline,
+                         int32_t device, int64_t max_batch, rrl_actor_t **out);
+int32_t rrl_actor_destroy(rrl_actor_t *a);
+int32_t rrl_actor_set_params(rrl_actor_t *a, int32_t which, const float *flat, int64_t n);
+/* One batched step on host buffers: act int64 [batch], logp_a f32 [batch] (= logits[i, act_i]),
+ * v f32 [batch] (NULL without baseline).  Sampling: inverse-CDF on softmax(logits) with one
+ * Philox4x32-10 uniform per env keyed by (seed, offset + env index).  probs/logits may be NULL. */
+int32_t rrl_actor_step(rrl_actor_t *a, const float *obs, const float *mask, int64_t batch,
+                       uint64_t seed, uint64_t offset, int64_t *act, float *logp_a, float *v,
+                       float *probs, float *logits);
+/* Same with device pointers; force_act (device, may be NULL) replaces the sampled action. */
+int32_t rrl_actor_step_device(rrl_actor_t *a, const float *obs, const float *mask, int64_t batch,
+                              uint64_t seed, uint64_t offset, const int64_t *force_act,
+                              int64_t *act, float *logp_a, float *v, float *probs, float *logits);
+const char *rrl_actor_last_error(const rrl_actor_t *a);
+
+/* ---- stateless device operators (for callers that own their device memory) ----------------- */
+/* Scratch the scan needs for n transitions (tile descriptors for the single-pass look-back). */
+int32_t rrl_scan_workspace_bytes(int64_t n, size_t *bytes);
+/* finish_path over all closed paths + adv statistics, everything device-resident except scalars.
+ * rew/val/adv/ret: [n_total] f32, 16-byte aligned; offsets: [n_ep+1] int64; last_vals: [n_ep] f32.
+ * stats_out (device, 5 doubles): sum, sumsq, n, mean(f32 value), std(f32 value) over adv[0, n_total).
+ * Elements >= offsets[n_ep] (unfinished tail) keep their adv/ret. stream = cudaStream_t. */
+int32_t rrl_scan_device(const float *rew, const float *val, const int64_t *offsets,
+                        const float *last_vals, int64_t n_total, int64_t n_ep, double gamma,
+                        double lam, int32_t with_baseline, float *adv, float *ret,
+                        double *stats_out, void *workspace, size_t workspace_bytes, void *stream);
+/* out[i] = (adv[i] - mean) / std in f32, mean/std read from stats (device, as written above). */
+int32_t rrl_normalise_device(const float *adv, int64_t n, const double *stats, float *out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RELAYRL_B200_H */

@@ -1,0 +1,590 @@
+// K2/K3: reward-to-go + GAE-lambda as ONE segmented reverse scan, fused with the advantage
+// statistics, and the (optional) materialised normalisation.
+//
+// Replaces, per epoch, E calls of ReplayBuffer.finish_path (two scipy.signal.lfilter calls each;
+// relayrl_framework/src/native/python/algorithms/REINFORCE/replay_buffer.py:48-79,
+// _common/_algorithms/BaseReplayBuffer.py:12-27) and statistics_scalar + the normalisation in
+// ReplayBuffer.get (BaseReplayBuffer.py:30-53, replay_buffer.py:94,105).
+//
+// Data layout: rew/val/adv/ret are flat f32 [N] (the reference's SoA numpy buffers,
+// replay_buffer.py:20-28); offsets int64 [E+1] are the successive path_start_idx values;
+// last_vals f32 [E] are the terminal markers' rewards (REINFORCE.py:86).
+//
+// Algorithm: both recurrences y[t] = x[t] + c*y[t+1] are affine maps of the value carried in
+// from the right; maps compose associatively, and an episode end resets the carry (the map's
+// slope becomes 0).  One pass over HBM (16 B/transition with baseline, 12 B without):
+//   tile (2048 transitions/CTA, tiles handed out right-to-left by an atomic ticket)
+//     -> coalesced 128-bit loads into swizzled shared memory, blocked 8-per-thread reads
+//     -> episode ends of the tile found by a 32-ary warp search in `offsets`
+//     -> thread-serial map, warp-shuffle suffix scan, 8 warp maps through shared memory
+//     -> single-pass decoupled look-back across tiles (aggregate / inclusive descriptors)
+//     -> second thread-serial pass seeded with the carry, results staged through shared
+//        memory and written with coalesced 128-bit stores
+//     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64.
+// Arithmetic is float64 with float32 storage, as in the reference.
+#include "common.cuh"
+
+namespace rrl {
+
+namespace {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_VPT = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VPT;  // 2048 transitions per CTA
+constexpr int SCAN_WARPS = SCAN_THREADS / 32;
+constexpr int SCAN_SMEM_FLOATS = SCAN_TILE + SCAN_TILE / 8 + 8;
+
+// 4 floats of padding after every 32: blocked 8-per-thread LDS.128 reads become conflict-free
+__device__ __forceinline__ int sidx(int j) { return j + ((j >> 5) << 2); }
+
+struct Map {  // ret: y = br + ar * carry ; adv: y = ba + aa * carry
+    double ar, br, aa, ba;
+};
+
+// left∘right: `right` is applied first (it is nearer the end of the episode)
+__device__ __forceinline__ Map compose(const Map &l, const Map &r)
+{
+    Map o;
+    o.ar = l.ar * r.ar;
+    o.br = fma(l.ar, r.br, l.br);
+    o.aa = l.aa * r.aa;
+    o.ba = fma(l.aa, r.ba, l.ba);
+    return o;
+}
+
+__device__ __forceinline__ Map shfl_down_map(const Map &m, int d)
+{
+    Map o;
+    o.ar = __shfl_down_sync(0xffffffffu, m.ar, d);
+    o.br = __shfl_down_sync(0xffffffffu, m.br, d);
+    o.aa = __shfl_down_sync(0xffffffffu, m.aa, d);
+    o.ba = __shfl_down_sync(0xffffffffu, m.ba, d);
+    return o;
+}
+__device__ __forceinline__ Map shfl_up_map(const Map &m, int d)
+{
+    Map o;
+    o.ar = __shfl_up_sync(0xffffffffu, m.ar, d);
+    o.br = __shfl_up_sync(0xffffffffu, m.br, d);
+    o.aa = __shfl_up_sync(0xffffffffu, m.aa, d);
+    o.ba = __shfl_up_sync(0xffffffffu, m.ba, d);
+    return o;
+}
+__device__ __forceinline__ Map shfl_map(const Map &m, int src)
+{
+    Map o;
+    o.ar = __shfl_sync(0xffffffffu, m.ar, src);
+    o.br = __shfl_sync(0xffffffffu, m.br, src);
+    o.aa = __shfl_sync(0xffffffffu, m.aa, src);
+    o.ba = __shfl_sync(0xffffffffu, m.ba, src);
+    return o;
+}
+
+__device__ __forceinline__ int ld_acquire(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int *p, int v)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+struct ScanArgs {
+    const float *rew, *val;
+    const int64_t *offsets;
+    const float *last_vals;
+    int64_t n_scan;  // = offsets[n_ep]: end of the last closed path
+    int64_t n_ep;
+    double gamma, gl;
+    float *adv, *ret;
+    // workspace
+    int *ticket;
+    int *flags;      // 0 = nothing, 1 = aggregate published, 2 = inclusive published
+    Map *agg;        // tile map (carry-in from the right -> value at the tile's first element)
+    double2 *incl;   // final (ret, adv) at the tile's first element
+    double2 *partials;
+    int num_tiles;
+};
+
+// tile states published for the look-back
+constexpr int FLAG_AGG = 1, FLAG_INCL = 2;
+
+template <bool WB>
+__global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
+{
+    __shared__ __align__(16) float r_s[SCAN_SMEM_FLOATS];
+    __shared__ __align__(16) float v_s[SCAN_SMEM_FLOATS];
+    __shared__ float lv_s[SCAN_TILE];
+    __shared__ unsigned end_s[SCAN_TILE / 32];
+    __shared__ Map wm_s[SCAN_WARPS];
+    __shared__ double carry_s[2];
+    __shared__ double red_s[SCAN_WARPS][2];
+    __shared__ int tile_s;
+    __shared__ long long e0_s;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) tile_s = a.num_tiles - 1 - atomicAdd(a.ticket, 1);  // right-most tile first
+    if (tid < SCAN_TILE / 32) end_s[tid] = 0u;
+    __syncthreads();
+    const int tile = tile_s;
+    const int64_t t0 = (int64_t)tile * SCAN_TILE;
+    const int cnt = (int)min((int64_t)SCAN_TILE, a.n_scan - t0);
+
+    // ---- coalesced loads into swizzled shared memory ---------------------------------------
+#pragma unroll
+    for (int c = tid; c < SCAN_TILE / 4; c += SCAN_THREADS) {
+        const int64_t g = t0 + 4 * c;
+        float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = r4;
+        if (g + 3 < a.n_scan) {
+            r4 = __ldcs(reinterpret_cast<const float4 *>(a.rew + g));
+            if (WB) v4 = __ldcs(reinterpret_cast<const float4 *>(a.val + g));
+        } else {
+            float *rp = &r4.x, *vp = &v4.x;
+            for (int k = 0; k < 4; ++k)
+                if (g + k < a.n_scan) {
+                    rp[k] = a.rew[g + k];
+                    if (WB) vp[k] = a.val[g + k];
+                }
+        }
+        *reinterpret_cast<float4 *>(&r_s[sidx(4 * c)]) = r4;
+        if (WB) *reinterpret_cast<float4 *>(&v_s[sidx(4 * c)]) = v4;
+    }
+    if (WB && tid == 0) v_s[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < a.n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
+
+    // ---- first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0 ------------
+    if (warp == 0) {
+        long long lo = 1, hi = a.n_ep;
+        while (lo < hi) {
+            const long long span = hi - lo;
+            const long long p = lo + (span * (lane + 1)) / 33;
+            const bool gt = a.offsets[p] > t0;
+            const unsigned b = __ballot_sync(0xffffffffu, gt);
+            if (b == 0u) {
+                lo = lo + (span * 32) / 33 + 1;
+            } else {
+                const int f = __ffs(b) - 1;
+                hi = lo + (span * (f + 1)) / 33;
+                if (f > 0) lo = lo + (span * f) / 33 + 1;
+            }
+        }
+        if (lane == 0) e0_s = lo;
+    }
+    __syncthreads();
+    {
+        const int64_t t1 = t0 + cnt;
+        for (long long k = e0_s + tid; k <= a.n_ep; k += SCAN_THREADS) {
+            const int64_t b = a.offsets[k];
+            if (b > t1) break;
+            if (b > a.offsets[k - 1]) {  // a non-empty path ends at b-1
+                const int pos = (int)(b - 1 - t0);
+                atomicOr(&end_s[pos >> 5], 1u << (pos & 31));
+                lv_s[pos] = a.last_vals[k - 1];
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- blocked reads: SCAN_VPT consecutive transitions per thread ---------------------------
+    const int j0 = tid * SCAN_VPT;
+    float r[SCAN_VPT], v[SCAN_VPT];
+    {
+        const float4 ra = *reinterpret_cast<const float4 *>(&r_s[sidx(j0)]);
+        const float4 rb = *reinterpret_cast<const float4 *>(&r_s[sidx(j0) + 4]);
+        r[0] = ra.x, r[1] = ra.y, r[2] = ra.z, r[3] = ra.w, r[4] = rb.x, r[5] = rb.y, r[6] = rb.z, r[7] = rb.w;
+        if (WB) {
+            const float4 va = *reinterpret_cast<const float4 *>(&v_s[sidx(j0)]);
+            const float4 vb = *reinterpret_cast<const float4 *>(&v_s[sidx(j0) + 4]);
+            v[0] = va.x, v[1] = va.y, v[2] = va.z, v[3] = va.w, v[4] = vb.x, v[5] = vb.y, v[6] = vb.z, v[7] = vb.w;
+        }
+    }
+    const float v_edge = WB ? v_s[sidx(j0 + SCAN_VPT)] : 0.f;
+    const unsigned eb = (end_s[j0 >> 5] >> (j0 & 31)) & 0xffu;
+    const bool open_right = ((end_s[(cnt - 1) >> 5] >> ((cnt - 1) & 31)) & 1u) == 0u;
+
+    // ---- pass 1: this thread's map ------------------------------------------------------------
+    Map m;
+    {
+        double ret_n = 0.0, adv_n = 0.0, v_n = (double)v_edge, ar = 1.0, aa = 1.0;
+#pragma unroll
+        for (int k = SCAN_VPT - 1; k >= 0; --k) {
+            if ((eb >> k) & 1u) {
+                // with baseline the marker's reward bootstraps both recurrences
+                // (replay_buffer.py:66-73); without it is ignored (replay_buffer.py:75-77)
+                const double lvk = (double)lv_s[j0 + k];
+                ret_n = WB ? lvk : 0.0;
+                adv_n = 0.0;
+                v_n = lvk;
+                ar = 0.0;
+                aa = 0.0;
+            }
+            const double rr = (double)r[k];
+            const double delta = WB ? (fma(a.gamma, v_n, rr) - (double)v[k]) : rr;
+            adv_n = fma(a.gl, adv_n, delta);
+            ret_n = fma(a.gamma, ret_n, rr);
+            ar *= a.gamma;
+            aa *= a.gl;
+            if (WB) v_n = (double)v[k];
+        }
+        m.ar = ar, m.br = ret_n, m.aa = aa, m.ba = adv_n;
+    }
+
+    // ---- warp suffix scan of the maps (lane l: M_l∘M_{l+1}∘...∘M_31) ----------------------------
+    Map S = m;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const Map o = shfl_down_map(S, d);
+        if (lane + d < 32) S = compose(S, o);
+    }
+    Map Ex = shfl_down_map(S, 1);  // maps of the lanes to the right of this one
+    if (lane == 31) Ex.ar = 1.0, Ex.br = 0.0, Ex.aa = 1.0, Ex.ba = 0.0;
+    if (lane == 0) wm_s[warp] = S;
+    __syncthreads();  // (also: every thread has finished reading r_s / v_s)
+
+    Map Wsuf;  // maps of the warps to the right of this one
+    Wsuf.ar = 1.0, Wsuf.br = 0.0, Wsuf.aa = 1.0, Wsuf.ba = 0.0;
+    for (int w = warp + 1; w < SCAN_WARPS; ++w) Wsuf = compose(Wsuf, wm_s[w]);
+
+    // ---- publish the tile, fetch the carry from the tiles to the right -----------------------
+    if (warp == 0) {
+        const Map T = compose(wm_s[0], Wsuf);
+        const bool closed = (T.ar == 0.0 && T.aa == 0.0);  // value at the tile's first element is final
+        if (lane == 0) {
+            if (closed) {
+                a.incl[tile] = make_double2(T.br, T.ba);
+                st_release(&a.flags[tile], FLAG_INCL);
+            } else {
+                a.agg[tile] = T;
+                st_release(&a.flags[tile], FLAG_AGG);
+            }
+        }
+        double cr = 0.0, ca = 0.0;
+        if (open_right) {  // the right-most path of this tile continues in the next tile
+            Map acc;
+            acc.ar = 1.0, acc.br = 0.0, acc.aa = 1.0, acc.ba = 0.0;
+            int base = tile + 1;
+            while (true) {
+                const int k = base + lane;
+                Map q;
+                q.ar = 0.0, q.br = 0.0, q.aa = 0.0, q.ba = 0.0;
+                if (k < a.num_tiles) {
+                    int f;
+                    do {
+                        f = ld_acquire(&a.flags[k]);
+                    } while (f == 0);
+                    if (f == FLAG_INCL) {
+                        const double2 iv = __ldcg(&a.incl[k]);
+                        q.br = iv.x, q.ba = iv.y;
+                    } else {
+                        const double2 *ap = reinterpret_cast<const double2 *>(&a.agg[k]);
+                        const double2 lo2 = __ldcg(ap), hi2 = __ldcg(ap + 1);
+                        q.ar = lo2.x, q.br = lo2.y, q.aa = hi2.x, q.ba = hi2.y;
+                    }
+                }
+                __syncwarp();
+                // ordered prefix over the window: P_l = q_0∘q_1∘...∘q_l
+                Map P = q;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const Map o = shfl_up_map(P, d);
+                    if (lane >= d) P = compose(o, P);
+                }
+                const unsigned z = __ballot_sync(0xffffffffu, P.ar == 0.0 && P.aa == 0.0);
+                if (z != 0u) {
+                    const Map Ps = shfl_map(P, __ffs(z) - 1);
+                    const Map R = compose(acc, Ps);
+                    cr = R.br, ca = R.ba;
+                    break;
+                }
+                acc = compose(acc, shfl_map(P, 31));
+                base += 32;
+            }
+        }
+        if (lane == 0) {
+            if (!closed) {
+                a.incl[tile] = make_double2(fma(T.ar, cr, T.br), fma(T.aa, ca, T.ba));
+                st_release(&a.flags[tile], FLAG_INCL);
+            }
+            carry_s[0] = cr, carry_s[1] = ca;
+        }
+    }
+    __syncthreads();
+
+    // ---- pass 2: final values, seeded with the carry ------------------------------------------
+    double s1 = 0.0, s2 = 0.0;
+    {
+        const double wr = fma(Wsuf.ar, carry_s[0], Wsuf.br), wa = fma(Wsuf.aa, carry_s[1], Wsuf.ba);
+        double ret_n = fma(Ex.ar, wr, Ex.br), adv_n = fma(Ex.aa, wa, Ex.ba), v_n = (double)v_edge;
+        float ao[SCAN_VPT], ro[SCAN_VPT];
+#pragma unroll
+        for (int k = SCAN_VPT - 1; k >= 0; --k) {
+            if ((eb >> k) & 1u) {
+                const double lvk = (double)lv_s[j0 + k];
+                ret_n = WB ? lvk : 0.0;
+                adv_n = 0.0;
+                v_n = lvk;
+            }
+            const double rr = (double)r[k];
+            const double delta = WB ? (fma(a.gamma, v_n, rr) - (double)v[k]) : rr;
+            adv_n = fma(a.gl, adv_n, delta);
+            ret_n = fma(a.gamma, ret_n, rr);
+            if (WB) v_n = (double)v[k];
+            ao[k] = (float)adv_n;
+            ro[k] = (float)ret_n;
+            if (j0 + k < cnt) {
+                const double x = (double)ao[k];
+                s1 += x;
+                s2 = fma(x, x, s2);
+            }
+        }
+        *reinterpret_cast<float4 *>(&r_s[sidx(j0)]) = make_float4(ao[0], ao[1], ao[2], ao[3]);
+        *reinterpret_cast<float4 *>(&r_s[sidx(j0) + 4]) = make_float4(ao[4], ao[5], ao[6], ao[7]);
+        *reinterpret_cast<float4 *>(&v_s[sidx(j0)]) = make_float4(ro[0], ro[1], ro[2], ro[3]);
+        *reinterpret_cast<float4 *>(&v_s[sidx(j0) + 4]) = make_float4(ro[4], ro[5], ro[6], ro[7]);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, d);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, d);
+    }
+    if (lane == 0) red_s[warp][0] = s1, red_s[warp][1] = s2;
+    __syncthreads();
+
+    // ---- coalesced 128-bit stores -------------------------------------------------------------
+#pragma unroll
+    for (int c = tid; c < SCAN_TILE / 4; c += SCAN_THREADS) {
+        const int64_t g = t0 + 4 * c;
+        const float4 a4 = *reinterpret_cast<const float4 *>(&r_s[sidx(4 * c)]);
+        const float4 r4 = *reinterpret_cast<const float4 *>(&v_s[sidx(4 * c)]);
+        if (g + 3 < a.n_scan) {
+            __stcs(reinterpret_cast<float4 *>(a.adv + g), a4);
+            __stcs(reinterpret_cast<float4 *>(a.ret + g), r4);
+        } else {
+            const float *ap = &a4.x, *rp = &r4.x;
+            for (int k = 0; k < 4; ++k)
+                if (g + k < a.n_scan) {
+                    a.adv[g + k] = ap[k];
+                    a.ret[g + k] = rp[k];
+                }
+        }
+    }
+    if (tid == 0) {
+        double t1 = 0.0, t2 = 0.0;
+        for (int w = 0; w < SCAN_WARPS; ++w) t1 += red_s[w][0], t2 += red_s[w][1];
+        a.partials[tile] = make_double2(t1, t2);
+    }
+}
+
+// mean/std exactly as statistics_scalar defines them (BaseReplayBuffer.py:41-47): f32 mean,
+// population variance about that f32 mean, f32 std, no epsilon.
+__device__ void finalize_stats(double *stats)
+{
+    const double sum = stats[0], sumsq = stats[1], n = stats[2];
+    const float mean_f = (float)(sum / n);
+    const double mm = (double)mean_f;
+    double m2 = sumsq - 2.0 * mm * sum + n * mm * mm;
+    if (m2 < 0.0) m2 = 0.0;
+    const float std_f = (float)sqrt(m2 / n);
+    stats[3] = (double)mean_f;
+    stats[4] = (double)std_f;
+}
+
+// Sums the per-tile partials in a fixed order (deterministic), adds the unfinished tail
+// [n_scan, n_total) which keeps whatever adv it held.
+__global__ void __launch_bounds__(1024) stats_reduce_kernel(const double2 *partials, int num_tiles,
+                                                            const float *adv, int64_t n_scan,
+                                                            int64_t n_total, double *stats, int finalize)
+{
+    __shared__ double s_a[1024], s_b[1024];
+    const int tid = threadIdx.x;
+    double a = 0.0, b = 0.0;
+    for (int i = tid; i < num_tiles; i += 1024) {
+        const double2 p = partials[i];
+        a += p.x, b += p.y;
+    }
+    for (int64_t i = n_scan + tid; i < n_total; i += 1024) {
+        const double x = (double)adv[i];
+        a += x, b = fma(x, x, b);
+    }
+    s_a[tid] = a, s_b[tid] = b;
+    __syncthreads();
+    for (int s = 512; s > 0; s >>= 1) {
+        if (tid < s) s_a[tid] += s_a[tid + s], s_b[tid] += s_b[tid + s];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        stats[0] = s_a[0], stats[1] = s_b[0], stats[2] = (double)n_total;
+        if (finalize) finalize_stats(stats);
+    }
+}
+
+__global__ void stats_finalize_kernel(double *stats) { finalize_stats(stats); }
+
+// gathered: [nranks][4] (sum, sumsq, n, n_episodes) in rank order -> identical result on every rank
+__global__ void stats_merge_kernel(const double *gathered, int nranks, double *stats)
+{
+    double a = 0.0, b = 0.0, n = 0.0, e = 0.0;
+    for (int r = 0; r < nranks; ++r)
+        a += gathered[4 * r], b += gathered[4 * r + 1], n += gathered[4 * r + 2], e += gathered[4 * r + 3];
+    stats[0] = a, stats[1] = b, stats[2] = n, stats[5] = e;
+    finalize_stats(stats);
+}
+
+// K3 (materialised): out = (adv - mean) / std in f32 with IEEE division (replay_buffer.py:105)
+__global__ void __launch_bounds__(256) normalise_kernel(const float *__restrict__ adv, int64_t n,
+                                                       const double *__restrict__ stats,
+                                                       float *__restrict__ out)
+{
+    const float mean = (float)stats[3], sd = (float)stats[4];
+    const int64_t n4 = n >> 2;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 x = __ldcs(reinterpret_cast<const float4 *>(adv) + i);
+        x.x = __fdiv_rn(x.x - mean, sd);
+        x.y = __fdiv_rn(x.y - mean, sd);
+        x.z = __fdiv_rn(x.z - mean, sd);
+        x.w = __fdiv_rn(x.w - mean, sd);
+        __stcs(reinterpret_cast<float4 *>(out) + i, x);
+    }
+    for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        out[i] = __fdiv_rn(adv[i] - mean, sd);
+}
+
+// K1b: wire f64 payload -> f32 buffer columns
+__global__ void __launch_bounds__(256) cvt_f64_f32_kernel(const double *__restrict__ src,
+                                                         float *__restrict__ dst, int64_t n)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        dst[i] = (float)src[i];
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct WsLayout {
+    size_t ticket, flags, agg, incl, partials, total;
+    int num_tiles;
+};
+
+WsLayout ws_layout(int64_t n)
+{
+    WsLayout w;
+    w.num_tiles = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+    if (w.num_tiles < 1) w.num_tiles = 1;
+    size_t o = 0;
+    w.ticket = o, o += 256;
+    w.flags = o, o += align_up(sizeof(int) * (size_t)w.num_tiles, 256);
+    w.agg = o, o += align_up(sizeof(Map) * (size_t)w.num_tiles, 256);
+    w.incl = o, o += align_up(sizeof(double2) * (size_t)w.num_tiles, 256);
+    w.partials = o, o += align_up(sizeof(double2) * (size_t)w.num_tiles, 256);
+    w.total = o;
+    return w;
+}
+
+}  // namespace
+
+size_t scan_workspace_bytes(int64_t n) { return ws_layout(n).total; }
+
+int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, const float *last_vals,
+                    int64_t n_total, int64_t n_ep, double gamma, double lam, bool with_baseline,
+                    float *adv, float *ret, double *stats_out, void *workspace, size_t workspace_bytes,
+                    bool finalize_stats_flag, int64_t n_scan_known, cudaStream_t stream, ErrBuf &err,
+                    int *launches)
+{
+    if (n_total < 0 || n_ep < 0) {
+        err.set("scan: negative sizes");
+        return RRL_EINVAL;
+    }
+    if ((((uintptr_t)rew | (uintptr_t)adv | (uintptr_t)ret | (with_baseline ? (uintptr_t)val : 0)) & 15) != 0) {
+        err.set("scan: rew/val/adv/ret must be 16-byte aligned");
+        return RRL_EINVAL;
+    }
+    const WsLayout w = ws_layout(n_total);
+    if (workspace == nullptr || workspace_bytes < w.total) {
+        err.set("scan: workspace too small (%zu < %zu bytes)", workspace_bytes, w.total);
+        return RRL_EINVAL;
+    }
+    // n_scan = offsets[n_ep] lives on the device; the host knows it only through the caller.
+    // The learner passes host-tracked offsets, the stateless entry point reads it back once.
+    int64_t n_scan = n_scan_known >= 0 ? n_scan_known : 0;
+    if (n_ep > 0 && n_scan_known < 0) {
+        RRL_CUDA_OK(cudaMemcpyAsync(&n_scan, offsets + n_ep, sizeof(int64_t), cudaMemcpyDeviceToHost, stream), err);
+        RRL_CUDA_OK(cudaStreamSynchronize(stream), err);
+        if (n_scan < 0 || n_scan > n_total) {
+            err.set("scan: offsets[n_ep] = %lld outside [0, %lld]", (long long)n_scan, (long long)n_total);
+            return RRL_EINVAL;
+        }
+    }
+    char *base = static_cast<char *>(workspace);
+    ScanArgs a;
+    a.rew = rew, a.val = val, a.offsets = offsets, a.last_vals = last_vals;
+    a.n_scan = n_scan, a.n_ep = n_ep;
+    a.gamma = gamma, a.gl = gamma * lam;  // the reference forms gamma * lam in double (replay_buffer.py:70)
+    a.adv = adv, a.ret = ret;
+    a.ticket = reinterpret_cast<int *>(base + w.ticket);
+    a.flags = reinterpret_cast<int *>(base + w.flags);
+    a.agg = reinterpret_cast<Map *>(base + w.agg);
+    a.incl = reinterpret_cast<double2 *>(base + w.incl);
+    a.partials = reinterpret_cast<double2 *>(base + w.partials);
+    a.num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
+    if (a.num_tiles > 0) {
+        // ticket + flags must start at zero
+        RRL_CUDA_OK(cudaMemsetAsync(base, 0, w.agg, stream), err);
+        if (with_baseline)
+            scan_kernel<true><<<a.num_tiles, SCAN_THREADS, 0, stream>>>(a);
+        else
+            scan_kernel<false><<<a.num_tiles, SCAN_THREADS, 0, stream>>>(a);
+        RRL_CUDA_OK(cudaGetLastError(), err);
+        if (launches) *launches += 1;
+    }
+    if (stats_out) {
+        stats_reduce_kernel<<<1, 1024, 0, stream>>>(a.partials, a.num_tiles, adv, n_scan, n_total, stats_out,
+                                                    finalize_stats_flag ? 1 : 0);
+        RRL_CUDA_OK(cudaGetLastError(), err);
+        if (launches) *launches += 1;
+    }
+    return RRL_OK;
+}
+
+int32_t stats_finalize_launch(double *stats, cudaStream_t stream, ErrBuf &err)
+{
+    stats_finalize_kernel<<<1, 1, 0, stream>>>(stats);
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    return RRL_OK;
+}
+
+int32_t stats_merge_launch(const double *gathered, int nranks, double *stats, cudaStream_t stream, ErrBuf &err)
+{
+    stats_merge_kernel<<<1, 1, 0, stream>>>(gathered, nranks, stats);
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    return RRL_OK;
+}
+
+int32_t normalise_launch(const float *adv, int64_t n, const double *stats, float *out, cudaStream_t stream,
+                         ErrBuf &err)
+{
+    if (n <= 0) return RRL_OK;
+    if ((((uintptr_t)adv | (uintptr_t)out) & 15) != 0) {
+        err.set("normalise: adv/out must be 16-byte aligned");
+        return RRL_EINVAL;
+    }
+    int64_t blocks = (n / 4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks < 1) blocks = 1;
+    normalise_kernel<<<(int)blocks, 256, 0, stream>>>(adv, n, stats, out);
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    return RRL_OK;
+}
+
+int32_t cvt_f64_f32_launch(const double *src, float *dst, int64_t n, cudaStream_t stream, ErrBuf &err)
+{
+    if (n <= 0) return RRL_OK;
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    cvt_f64_f32_kernel<<<(int)blocks, 256, 0, stream>>>(src, dst, n);
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    return RRL_OK;
+}
+
+}  // namespace rrl

@@ -14,6 +14,10 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    so = os.path.join(PKG, "relayrl_b200", "librelayrl_b200.so")
+    if not os.path.exists(so):  # nvcc cross-compiles sm_100a without a GPU
+        import subprocess
+        subprocess.check_call(["make", "-s", "-j8", "-C", os.path.join(PKG, "csrc")])
 
 
 @pytest.fixture(scope="session")

@@ -1,0 +1,230 @@
+"""GPU parity of the fused learner (K4-K7) through the C ABI and through the drop-in algorithm
+class, against golden vectors produced by the unmodified reference and against the oracle.
+
+Tolerance: rel 1e-5 (north star) with the absolute floor the reference itself shows between
+thread counts (tests/test_oracle.py: ~7e-8 on weights after 81 Adam steps; 5e-7 used)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import PKG, load_golden
+from oracle import learner_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+W_RTOL, W_ATOL = 1e-5, 5e-7
+
+
+def _mk(g, iters=None):
+    from relayrl_b200 import Learner
+    d, A, H, wb = int(g["d"]), int(g["A"]), int(g["H"]), bool(g["with_baseline"])
+    L = Learner(d, A, 8192, hidden=H, with_baseline=wb, gamma=float(g["gamma"]), lam=float(g["lam"]),
+                pi_lr=float(g["pi_lr"]), vf_lr=float(g["vf_lr"]),
+                train_vf_iters=int(g["iters"]) if iters is None else iters)
+    L.set_params(0, g["pi0"])
+    if wb:
+        L.set_params(1, g["v0"])
+    return L, d, A, H, wb
+
+
+def _ingest_epoch(L, g, ep):
+    p = "e%d_" % ep
+    L.ingest(g[p + "in_obs"], g[p + "in_act"], g[p + "in_mask"], g[p + "in_rew"], g[p + "in_val"],
+             g[p + "in_logp"], g[p + "in_done"])
+
+
+@pytest.mark.parametrize("name", ["epoch_vf_h128", "epoch_vf_h64", "epoch_novf_h128"])
+def test_epoch_golden(name):
+    g = load_golden(name)
+    L, d, A, H, wb = _mk(g)
+    for ep in range(int(g["epochs"])):
+        p = "e%d_" % ep
+        _ingest_epoch(L, g, ep)
+        n, _ = L.finish()
+        assert np.array_equal(L.offsets(), g[p + "offsets"])
+        np.testing.assert_allclose(L.returns(n), g[p + "ret_raw"], rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(L.advantages(n, False), g[p + "adv_raw"], rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(L.advantages(n, True), g[p + "get_adv"], rtol=1e-5, atol=1e-5)
+        st = L.train_epoch()
+        assert st["n_transitions"] == n
+        np.testing.assert_allclose(st["loss_pi"], float(g[p + "LossPi"]), rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(st["kl"], float(g[p + "KL"]), rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(st["entropy"], float(g[p + "Entropy"]), rtol=1e-5, atol=1e-7)
+        assert st["delta_loss_pi"] == 0.0
+        np.testing.assert_allclose(L.get_params(0), g[p + "pi"], rtol=W_RTOL, atol=W_ATOL)
+        if wb:
+            np.testing.assert_allclose(st["loss_v"], float(g[p + "LossV"]), rtol=1e-5)
+            np.testing.assert_allclose(st["delta_loss_v"], float(g[p + "DeltaLossV"]), rtol=1e-4, atol=1e-6)
+            np.testing.assert_allclose(L.get_params(1), g[p + "v"], rtol=W_RTOL, atol=W_ATOL)
+    L.close()
+
+
+@pytest.mark.parametrize("name", ["epoch_vf_h128", "epoch_vf_h64", "epoch_novf_h128"])
+def test_gradients_vs_oracle_autograd(name):
+    g = load_golden(name)
+    L, d, A, H, wb = _mk(g)
+    _ingest_epoch(L, g, 0)
+    L.finish()
+    data = {k: torch.from_numpy(g["e0_get_" + k]) for k in ("obs", "act", "mask", "ret", "adv", "logp")}
+    ref = lo.train_epoch(lo.unflatten(g["pi0"], d, H, A), lo.unflatten(g["v0"], d, H, 1) if wb else None, data,
+                         float(g["pi_lr"]), float(g["vf_lr"]), 1, return_grads=True)
+    gp, (lpi, kl, ent) = L.eval_grad(0)
+    scale = np.abs(ref["pi_grad"].numpy()).max()
+    np.testing.assert_allclose(gp, ref["pi_grad"].numpy(), rtol=1e-5, atol=1e-6 * scale)
+    np.testing.assert_allclose(lpi, ref["LossPi"], rtol=1e-5, atol=1e-7)
+    if wb:
+        gv, (lv, _, _) = L.eval_grad(1)
+        scale = np.abs(ref["v_grad_first"].numpy()).max()
+        np.testing.assert_allclose(gv, ref["v_grad_first"].numpy(), rtol=1e-5, atol=1e-6 * scale)
+        np.testing.assert_allclose(lv, ref["LossVOld"], rtol=1e-5)
+    L.close()
+
+
+def test_larger_batch_vs_oracle_multi_tile():
+    """~70k transitions (more tiles than SMs, several f64 flush windows), d=8, A=4, masks."""
+    rng = np.random.default_rng(7)
+    d, A, H = 8, 4, 128
+    lens = rng.integers(5, 400, 350)
+    done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
+    n = len(done)
+    obs = rng.standard_normal((n, d)).astype(np.float32)
+    act = rng.integers(0, A, n).astype(np.float32)
+    mask = np.ones((n, A), np.float32)
+    off = rng.integers(0, A, n)
+    sel = (rng.random(n) < 0.2) & (off != act)
+    mask[np.flatnonzero(sel), off[sel]] = 0
+    rew = rng.uniform(-1, 1, n).astype(np.float32)
+    val = rng.standard_normal(n).astype(np.float32)
+    logp = rng.standard_normal(n).astype(np.float32)
+    O = lo.OracleLearner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=5, seed=3)
+    from relayrl_b200 import Learner
+    L = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=5)
+    L.set_params(0, lo.flatten(O.pi).numpy())
+    L.set_params(1, lo.flatten(O.v).numpy())
+    O.ingest(obs, act, mask, rew, val, logp, done)
+    L.ingest(obs, act, mask, rew, val, logp, done)
+    ref = O.train()
+    st = L.train_epoch()
+    np.testing.assert_allclose(st["loss_pi"], ref["LossPi"], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(st["loss_v"], ref["LossV"], rtol=1e-5)
+    np.testing.assert_allclose(st["loss_v_old"], ref["LossVOld"], rtol=1e-5)
+    np.testing.assert_allclose(st["entropy"], ref["Entropy"], rtol=1e-5)
+    np.testing.assert_allclose(L.get_params(0), lo.flatten(O.pi).numpy(), rtol=W_RTOL, atol=W_ATOL)
+    np.testing.assert_allclose(L.get_params(1), lo.flatten(O.v).numpy(), rtol=W_RTOL, atol=W_ATOL)
+    m, v, step = L.get_opt_state(1)
+    assert step == 5
+    sd = O._v_opt.state_dict()["state"]
+    m_ref = torch.cat([sd[i]["exp_avg"].reshape(-1) for i in range(6)]).numpy()
+    np.testing.assert_allclose(m, m_ref, rtol=1e-5, atol=1e-6 * np.abs(m_ref).max())
+    L.close()
+
+
+def test_log_softmax_mode_gradient():
+    """Opt-in textbook REINFORCE (logp = log_softmax); checked against torch autograd."""
+    from relayrl_b200 import Learner
+    rng = np.random.default_rng(11)
+    d, A, H, n = 4, 3, 64, 777
+    obs = rng.standard_normal((n, d)).astype(np.float32)
+    act = rng.integers(0, A, n).astype(np.float32)
+    mask = np.ones((n, A), np.float32)
+    rew = rng.uniform(-1, 1, n).astype(np.float32)
+    done = np.zeros(n + 1, np.uint8)
+    done[-1] = 1
+    pad = lambda a: np.concatenate([a, np.zeros((1,) + a.shape[1:], a.dtype)])
+    L = Learner(d, A, n + 8, hidden=H, with_baseline=False, logp_mode=1)
+    pi = lo.init_params(d, H, A, 5)
+    L.set_params(0, lo.flatten(pi).numpy())
+    L.ingest(pad(obs), pad(act), np.concatenate([mask, np.ones((1, A), np.float32)]), pad(rew), None, pad(rew), done)
+    L.finish()
+    adv = torch.from_numpy(L.advantages(n, True).copy())
+    g, (loss, _, _) = L.eval_grad(0)
+    ps = [p.clone().requires_grad_(True) for p in pi]
+    logits = lo.mlp3(ps, torch.from_numpy(obs)) + (torch.from_numpy(mask) - 1) * 1e8
+    lp = torch.log_softmax(logits, -1).gather(-1, torch.from_numpy(act).long()[:, None]).squeeze(-1)
+    ref_loss = -(lp * adv).mean()
+    ref_loss.backward()
+    ref_g = torch.cat([p.grad.reshape(-1) for p in ps]).numpy()
+    np.testing.assert_allclose(loss, ref_loss.item(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(g, ref_g, rtol=1e-4, atol=1e-6 * np.abs(ref_g).max())
+    L.close()
+
+
+def test_plugin_class_end_to_end(tmp_path):
+    """The drop-in algorithm class fed duck-typed trajectories like the reference worker does
+    (python_algorithm_reply.py:99-104), incl. the TorchScript hand-off contract
+    (agent_wrapper.rs:88-168)."""
+    sys.path.insert(0, os.path.join(PKG, "algorithms"))
+    import importlib
+    mod = importlib.import_module("REINFORCE_B200.REINFORCE_B200")
+    from oracle.ref_bridge import DuckAction, DuckTrajectory
+    g = load_golden("epoch_vf_h128")
+    cfg = tmp_path / "relayrl_config.json"
+    model = tmp_path / "server_model.pt"
+    cfg.write_text('{"algorithms": {"REINFORCE": {"with_vf_baseline": true, "traj_per_epoch": 1, '
+                   '"train_vf_iters": 80, "gamma": 0.98, "lam": 0.97, "pi_lr": 0.0003, "vf_lr": 0.001}}, '
+                   '"model_paths": {"server_model": "%s"}}' % model)
+    algo = mod.REINFORCE_B200(env_dir=str(tmp_path), config_path=str(cfg), obs_dim=4, act_dim=2, buf_size=8192)
+    algo.learner.set_params(0, g["pi0"])
+    algo.learner.set_params(1, g["v0"])
+    for ep in range(int(g["epochs"])):
+        p = "e%d_" % ep
+        acts = []
+        for i in range(len(g[p + "in_done"])):
+            if g[p + "in_done"][i]:
+                acts.append(DuckAction(rew=float(g[p + "in_rew"][i]), done=True))
+            else:
+                acts.append(DuckAction(g[p + "in_obs"][i], np.array([g[p + "in_act"][i]], np.float32),
+                                       g[p + "in_mask"][i], float(g[p + "in_rew"][i]),
+                                       {"logp_a": np.array([g[p + "in_logp"][i]], np.float32),
+                                        "v": np.float32(g[p + "in_val"][i])}, False))
+        assert algo.receive_trajectory(DuckTrajectory(acts)) is True
+        np.testing.assert_allclose(algo.last_stats["loss_pi"], float(g[p + "LossPi"]), rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(algo.learner.get_params(1), g[p + "v"], rtol=W_RTOL, atol=W_ATOL)
+    algo.save()
+    m = torch.jit.load(str(model))
+    assert m.get_input_dim() == 4 and m.get_output_dim() == 2
+    act, data = m.step(torch.zeros(1, 4), torch.zeros(1, 2))
+    assert isinstance(act, torch.Tensor) and len(data) > 0 and "logp_a" in data and "v" in data
+    sd = m.state_dict()
+    np.testing.assert_allclose(sd["policy.pi_network.2.weight"].numpy().reshape(-1),
+                               algo.learner.get_params(0)[4 * 128 + 128:4 * 128 + 128 + 128 * 128], rtol=0, atol=0)
+    assert os.path.exists(os.path.join(str(tmp_path), "logs"))
+
+
+def test_wire_action_ingest_safetensors():
+    """rrl_ingest_wire_action on blobs laid out as safetensors 0.5 writes them (action.rs:345,372-381)."""
+    import json
+    import struct
+
+    def blob(arr, name="tensor"):
+        arr = np.ascontiguousarray(arr)
+        dt = {np.dtype("float64"): "F64", np.dtype("float32"): "F32"}[arr.dtype]
+        hdr = json.dumps({name: {"dtype": dt, "shape": list(arr.shape), "data_offsets": [0, arr.nbytes]}},
+                         separators=(",", ":")).encode()
+        hdr += b" " * ((8 - len(hdr) % 8) % 8)
+        return struct.pack("<Q", len(hdr)) + hdr + arr.tobytes()
+
+    from relayrl_b200 import Learner
+    g = load_golden("epoch_vf_h128")
+    L, d, A, H, wb = _mk(g, iters=1)
+    p = "e0_"
+    n_in = len(g[p + "in_done"])
+    for i in range(n_in):
+        if g[p + "in_done"][i]:
+            L.ingest_wire_action(None, None, None, float(g[p + "in_rew"][i]), None, None, True)
+        else:
+            L.ingest_wire_action(blob(g[p + "in_obs"][i]), blob(np.array([g[p + "in_act"][i]], np.float32)),
+                                 blob(g[p + "in_mask"][i]), float(g[p + "in_rew"][i]),
+                                 blob(np.array(g[p + "in_val"][i], np.float32)),
+                                 blob(np.array([g[p + "in_logp"][i]], np.float32)), False)
+    n, _ = L.finish()
+    assert np.array_equal(L.offsets(), g[p + "offsets"])
+    np.testing.assert_allclose(L.returns(n), g[p + "ret_raw"], rtol=1e-6, atol=1e-6)
+    from relayrl_b200 import RelayRLB200Error
+    with pytest.raises(RelayRLB200Error) as e:
+        L.ingest_wire_action(b"\x05\x00", b"", b"", 0.0, b"", b"", False)
+    assert e.value.status == -6
+    L.close()
