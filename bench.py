@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py -- learner transitions/s of the RelayRL hot path on B200 (BASELINE.json metric).
+
+A step is ONE full learner epoch on one batch of synthetic trajectories:
+  ingest -> reward-to-go/GAE scan + statistics -> policy step -> train_vf_iters value steps
+(REINFORCE.receive_trajectory + train_model, reference REINFORCE.py:70-125).
+Workload (config.workload): REINFORCE with baseline, d=4, A=2, H=128, 80 value iterations, C3-style
+variable episode lengths, N = --n transitions per GPU (default 64 Mi = BASELINE's target batch).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--n N_PER_GPU] [--impl reference]
+Under torchrun (N > 1) every rank owns its own shard (weak scaling); gradients/statistics are
+all-reduced over NCCL inside the library.  One JSON line is printed by rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "relayrl-prototype_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+D, A, H, ITERS = 4, 2, 128, 80
+GAMMA, LAM = 0.98, 0.97
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return p["hbm_gbs"], p["bf16_tflops"], p["bf16_tflops_sustained"], "measured"
+    except Exception:
+        return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+def episode_lengths(rng, n):
+    """C3 mixture: 90 % U{1..1000}, 9 % U{1000..20000}, 1 % U{20000..2000000}; the last
+    episode is truncated to fit."""
+    parts, tot = [], 0
+    while tot < n:
+        k = 4096
+        u = rng.random(k)
+        L = np.where(u < 0.9, rng.integers(1, 1001, k), np.where(u < 0.99, rng.integers(1000, 20001, k),
+                                                                 rng.integers(20000, 2000001, k)))
+        parts.append(L)
+        tot += int(L.sum())
+    L = np.concatenate(parts).astype(np.int64)
+    c = np.cumsum(L)
+    m = int(np.searchsorted(c, n, side="left"))      # first episode whose end reaches n
+    L = L[:m + 1].copy()
+    L[m] = n - (int(c[m - 1]) if m > 0 else 0)
+    return L
+
+
+def make_stream(n, seed, pinned):
+    """Synthetic action stream of n transitions + one terminal marker per episode, SoA, host."""
+    import torch
+    rng = np.random.default_rng(seed)
+    lens = episode_lengths(rng, n)
+    E = len(lens)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    assert offsets[-1] == n
+    rows = n + E
+    g = torch.Generator().manual_seed(seed)
+
+    def buf(shape, dtype=torch.float32):
+        return torch.empty(shape, dtype=dtype, pin_memory=pinned)
+
+    obs = buf((rows, D)).normal_(generator=g)
+    act = buf((rows,)).copy_(torch.randint(0, A, (rows,), generator=g).float())
+    mask = buf((rows, A)).fill_(1.0)
+    # 10 % of rows have the action that was NOT taken masked out
+    sel = torch.rand(rows, generator=g) < 0.1
+    idx = torch.nonzero(sel).squeeze(1)
+    mask[idx, (1 - act[idx]).long()] = 0.0
+    rew = buf((rows,)).uniform_(-1, 1, generator=g)
+    val = buf((rows,)).normal_(generator=g)
+    logp = buf((rows,)).normal_(generator=g)
+    done = torch.zeros(rows, dtype=torch.uint8, pin_memory=pinned)
+    marker_rows = offsets[1:] + np.arange(E)          # row index of each terminal marker
+    done[torch.from_numpy(marker_rows)] = 1
+    return dict(obs=obs, act=act, mask=mask, rew=rew, val=val, logp=logp, done=done, rows=rows, n=n, E=E,
+                offsets=offsets, marker_rows=marker_rows)
+
+
+def device_columns(st, dev):
+    """Transitions only (markers removed), resident in HBM, + host offsets / last_vals."""
+    import torch
+    keep = torch.from_numpy(np.flatnonzero(st["done"].numpy() == 0))
+    cols = {k: st[k][keep].to(dev) for k in ("obs", "act", "mask", "rew", "val", "logp")}
+    last_vals = st["rew"].numpy()[st["marker_rows"]].copy()
+    return cols, st["offsets"], last_vals
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._halt = index, [], threading.Event()
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def finish(self):
+        self._halt.set()
+        self.join(timeout=6)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_baseline(sample_n, iters, threads, seed=7):
+    """The oracle port of the reference CPU learner (oracle/learner_oracle.py) on a bounded sample of
+    the same workload: ingest (segment + store) -> finish_path per episode -> get() -> train_model."""
+    import torch
+    from oracle import learner_oracle as lo
+    torch.set_num_threads(threads)
+    st = make_stream(sample_n, seed, pinned=False)
+    O = lo.OracleLearner(D, A, sample_n + 1, hidden=H, with_baseline=True, gamma=GAMMA, lam=LAM,
+                         train_vf_iters=iters, seed=1)
+    t0 = time.perf_counter()
+    O.ingest(st["obs"].numpy(), st["act"].numpy(), st["mask"].numpy(), st["rew"].numpy(), st["val"].numpy(),
+             st["logp"].numpy(), st["done"].numpy())
+    O.train()
+    dt = time.perf_counter() - t0
+    return sample_n / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU learner (oracle port; the reference is Python and
+    cannot travel to the GPU box) on the host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = args.ref_sample
+    times = []
+    for i in range(args.warmup + args.steps):
+        tps, dt = cpu_baseline(sample, ITERS, threads, seed=7 + i)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1000.0 * sum(times) / len(times)
+    value = sample / (ms / 1000.0)
+    sample_desc = "%d transitions (C3 length mixture), full epoch with %d value iterations, per step" % (sample, ITERS)
+    print(json.dumps({
+        "impl": "reference", "metric": "learner transitions/sec", "value": value, "unit": "transitions/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, sample),
+        "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": threads, "kind": "port",
+                         "sample": sample_desc},
+        "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def workload_config(args, n):
+    return {"workload": "REINFORCE_with_baseline epoch: ingest+scan+normalise+1 policy step+%d value steps; "
+                        "d=%d A=%d H=%d; %d transitions per GPU; C3 episode-length mixture" % (ITERS, D, A, H, n),
+            "transitions_per_gpu": n, "obs_dim": D, "act_dim": A, "hidden": H, "train_vf_iters": ITERS,
+            "l2": "inputs (%.1f GB per epoch pass) exceed the 126 MB L2" % (n * 4 * (D + A + 6) / 1e9),
+            "parallelism": "dp%d" % args.gpus}
+
+
+def run_ours(args):
+    import torch
+    from relayrl_b200 import Learner, _lib, nccl_unique_id, scan_device, scan_workspace_bytes
+    from relayrl_b200._lib import BatchView
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist = None
+    nccl_id = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.tensor(list(nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        nccl_id = bytes(idt.cpu().tolist())
+
+    n = args.n
+    st = make_stream(n, 64 + rank, pinned=True)
+    L = Learner(D, A, n + 1, hidden=H, with_baseline=True, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS,
+                device=local, rank=rank, nranks=world, nccl_id=nccl_id)
+    from oracle import learner_oracle as lo   # only for the (deterministic) initial weights
+    L.set_params(0, lo.flatten(lo.init_params(D, H, A, 1)).numpy())
+    L.set_params(1, lo.flatten(lo.init_params(D, H, 1, 2)).numpy())
+    cols, offsets, last_vals = device_columns(st, dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step_device():
+        L.ingest_device(cols["obs"], cols["act"], cols["mask"], cols["rew"], cols["val"], cols["logp"], n, offsets,
+                        last_vals)
+        return L.train_epoch()
+
+    view = BatchView(st["obs"].data_ptr(), st["act"].data_ptr(), st["mask"].data_ptr(), st["rew"].data_ptr(),
+                     st["val"].data_ptr(), st["logp"].data_ptr(), st["done"].data_ptr(), st["rows"], _lib.RRL_F32,
+                     _lib.RRL_F32)
+
+    def step_e2e():
+        L.ingest_raw(view)          # pinned host -> HBM inside the timed region
+        return L.train_epoch()      # stats come back to the host (D2H) inside the call
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        t0 = time.perf_counter()
+        stats = [fn() for _ in range(steps)]
+        barrier()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = t.item()
+        return dt, stats
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dt, stats = timed(step_device, args.steps, args.warmup)
+    clocks = sampler.finish() if rank == 0 else None
+    dt_e2e, stats_e2e = timed(step_e2e, max(1, min(args.steps, 2)), 1)
+    e2e_steps = max(1, min(args.steps, 2))
+
+    # the scan alone, CUDA events on the stream it is launched on (torch's current stream)
+    ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    adv, ret = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    sstats = torch.zeros(8, dtype=torch.float64, device=dev)
+    d_off, d_lv = torch.from_numpy(offsets).to(dev), torch.from_numpy(last_vals).to(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    reps = 10
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    for i in range(3 + reps):
+        if i >= 3:
+            e0[i - 3].record()
+        scan_device(cols["rew"], cols["val"], d_off, d_lv, n, len(last_vals), GAMMA, LAM, True, adv, ret, sstats, ws,
+                    stream=stream)
+        if i >= 3:
+            e1[i - 3].record()
+    torch.cuda.synchronize()
+    scan_ms = sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    hbm, bf16_burst, bf16_sust, which = peaks()
+    ms = 1000.0 * dt / args.steps
+    total_n = n * world
+    value = total_n / (dt / args.steps)
+    ms_e2e = 1000.0 * dt_e2e / e2e_steps
+    s = stats[-1]
+    # dominant kernel: the fused value-net forward+backward pass (80 launches per step)
+    flops_per_launch = 6.0 * (D * H + H * H + H) * n
+    value_launch_ms = sum(x["ms_value"] for x in stats) / len(stats) / ITERS
+    achieved_tf = flops_per_launch / (value_launch_ms * 1e-3) / 1e12
+    scan_gbs = 16.0 * n / (scan_ms * 1e-3) / 1e9
+    cpu_threads = os.cpu_count() or 1
+    cpu_tps, cpu_dt = cpu_baseline(args.cpu_sample, ITERS, cpu_threads)
+    line = {
+        "metric": "learner transitions/sec", "value": value, "unit": "transitions/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
+        "e2e": {"value": total_n / (ms_e2e / 1000.0), "unit": "transitions/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": int(n * 4 * (D + A + 4)), "d2h_bytes_per_step": int(C.sizeof(_lib.EpochStats) + 112)},
+        "gpu_launches": int(sum(x["kernel_launches"] for x in stats)),
+        "clocks": clocks,
+        "roofline": {"kernel": "mlp_tile_kernel<128,VALUE,grad> (fused value fwd+bwd, fp32 CUDA cores)",
+                     "bound": "tensor", "achieved": achieved_tf, "peak": bf16_sust, "unit": "TFLOP/s",
+                     "frac": achieved_tf / bf16_sust, "traffic": None, "peak_source": which + " bf16 sustained",
+                     "flops_per_launch": flops_per_launch, "launch_ms": value_launch_ms,
+                     "note": "fp32-accurate math on CUDA cores; FP32 FMA peak of the part is ~75 TFLOP/s"},
+        "roofline_scan": {"kernel": "scan_kernel<with_baseline>", "bound": "hbm", "achieved": scan_gbs, "peak": hbm,
+                          "unit": "GB/s", "frac": scan_gbs / hbm, "traffic": None, "peak_source": which,
+                          "bytes_per_transition": 16, "launch_ms": scan_ms},
+        "stage_ms": {"scan": s["ms_scan"], "policy": s["ms_policy"], "value": s["ms_value"]},
+        "cpu_baseline": {"value": cpu_tps, "unit": "transitions/s", "cores": cpu_threads, "kind": "port",
+                         "sample": "%d transitions, full epoch with %d value iterations, %.1f s" % (args.cpu_sample, ITERS, cpu_dt)},
+        "losses": {"loss_pi": s["loss_pi"], "loss_v": s["loss_v"], "entropy": s["entropy"]},
+    }
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--n", type=int, default=1 << 26, help="transitions per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-sample", type=int, default=1 << 17)
+    ap.add_argument("--ref-sample", type=int, default=1 << 17)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -95,8 +95,7 @@ struct ScanArgs {
     const float *rew, *val;
     const int64_t *offsets;
     const float *last_vals;
-    int64_t n_scan;  // = offsets[n_ep]: end of the last closed path
-    int64_t n_ep;
+    int64_t n_ep;    // closed paths; the scan covers [0, offsets[n_ep]) (read on the device)
     double gamma, gl;
     float *adv, *ret;
     // workspace
@@ -105,7 +104,6 @@ struct ScanArgs {
     Map *agg;        // tile map (carry-in from the right -> value at the tile's first element)
     double2 *incl;   // final (ret, adv) at the tile's first element
     double2 *partials;
-    int num_tiles;
 };
 
 // tile states published for the look-back
@@ -125,25 +123,28 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
     __shared__ long long e0_s;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) tile_s = a.num_tiles - 1 - atomicAdd(a.ticket, 1);  // right-most tile first
+    const int64_t n_scan = a.offsets[a.n_ep];  // end of the last closed path
+    const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
+    if (tid == 0) tile_s = num_tiles - 1 - atomicAdd(a.ticket, 1);  // right-most tile first
     if (tid < SCAN_TILE / 32) end_s[tid] = 0u;
     __syncthreads();
     const int tile = tile_s;
+    if (tile < 0) return;  // the grid is sized for n_total; CTAs beyond the scanned range have no work
     const int64_t t0 = (int64_t)tile * SCAN_TILE;
-    const int cnt = (int)min((int64_t)SCAN_TILE, a.n_scan - t0);
+    const int cnt = (int)min((int64_t)SCAN_TILE, n_scan - t0);
 
     // ---- coalesced loads into swizzled shared memory ---------------------------------------
 #pragma unroll
     for (int c = tid; c < SCAN_TILE / 4; c += SCAN_THREADS) {
         const int64_t g = t0 + 4 * c;
         float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = r4;
-        if (g + 3 < a.n_scan) {
+        if (g + 3 < n_scan) {
             r4 = __ldcs(reinterpret_cast<const float4 *>(a.rew + g));
             if (WB) v4 = __ldcs(reinterpret_cast<const float4 *>(a.val + g));
         } else {
             float *rp = &r4.x, *vp = &v4.x;
             for (int k = 0; k < 4; ++k)
-                if (g + k < a.n_scan) {
+                if (g + k < n_scan) {
                     rp[k] = a.rew[g + k];
                     if (WB) vp[k] = a.val[g + k];
                 }
@@ -151,7 +152,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         *reinterpret_cast<float4 *>(&r_s[sidx(4 * c)]) = r4;
         if (WB) *reinterpret_cast<float4 *>(&v_s[sidx(4 * c)]) = v4;
     }
-    if (WB && tid == 0) v_s[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < a.n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
+    if (WB && tid == 0) v_s[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
 
     // ---- first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0 ------------
     if (warp == 0) {
@@ -268,7 +269,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
                 const int k = base + lane;
                 Map q;
                 q.ar = 0.0, q.br = 0.0, q.aa = 0.0, q.ba = 0.0;
-                if (k < a.num_tiles) {
+                if (k < num_tiles) {
                     int f;
                     do {
                         f = ld_acquire(&a.flags[k]);
@@ -357,13 +358,13 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         const int64_t g = t0 + 4 * c;
         const float4 a4 = *reinterpret_cast<const float4 *>(&r_s[sidx(4 * c)]);
         const float4 r4 = *reinterpret_cast<const float4 *>(&v_s[sidx(4 * c)]);
-        if (g + 3 < a.n_scan) {
+        if (g + 3 < n_scan) {
             __stcs(reinterpret_cast<float4 *>(a.adv + g), a4);
             __stcs(reinterpret_cast<float4 *>(a.ret + g), r4);
         } else {
             const float *ap = &a4.x, *rp = &r4.x;
             for (int k = 0; k < 4; ++k)
-                if (g + k < a.n_scan) {
+                if (g + k < n_scan) {
                     a.adv[g + k] = ap[k];
                     a.ret[g + k] = rp[k];
                 }
@@ -392,10 +393,12 @@ __device__ void finalize_stats(double *stats)
 
 // Sums the per-tile partials in a fixed order (deterministic), adds the unfinished tail
 // [n_scan, n_total) which keeps whatever adv it held.
-__global__ void __launch_bounds__(1024) stats_reduce_kernel(const double2 *partials, int num_tiles,
-                                                            const float *adv, int64_t n_scan,
+__global__ void __launch_bounds__(1024) stats_reduce_kernel(const double2 *partials, const int64_t *offsets,
+                                                            int64_t n_ep, const float *adv,
                                                             int64_t n_total, double *stats, int finalize)
 {
+    const int64_t n_scan = n_ep > 0 ? offsets[n_ep] : 0;
+    const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
     __shared__ double s_a[1024], s_b[1024];
     const int tid = threadIdx.x;
     double a = 0.0, b = 0.0;
@@ -505,21 +508,18 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
         err.set("scan: workspace too small (%zu < %zu bytes)", workspace_bytes, w.total);
         return RRL_EINVAL;
     }
-    // n_scan = offsets[n_ep] lives on the device; the host knows it only through the caller.
-    // The learner passes host-tracked offsets, the stateless entry point reads it back once.
-    int64_t n_scan = n_scan_known >= 0 ? n_scan_known : 0;
-    if (n_ep > 0 && n_scan_known < 0) {
-        RRL_CUDA_OK(cudaMemcpyAsync(&n_scan, offsets + n_ep, sizeof(int64_t), cudaMemcpyDeviceToHost, stream), err);
-        RRL_CUDA_OK(cudaStreamSynchronize(stream), err);
-        if (n_scan < 0 || n_scan > n_total) {
-            err.set("scan: offsets[n_ep] = %lld outside [0, %lld]", (long long)n_scan, (long long)n_total);
-            return RRL_EINVAL;
-        }
+    // The scan covers [0, offsets[n_ep]).  When the caller knows that bound (the learner tracks
+    // offsets on the host) the grid is sized exactly; otherwise it is sized for n_total and the
+    // kernel, which reads offsets[n_ep] itself, retires the surplus CTAs -- no host round trip.
+    if (n_scan_known > n_total) {
+        err.set("scan: offsets[n_ep] = %lld exceeds n_total = %lld", (long long)n_scan_known, (long long)n_total);
+        return RRL_EINVAL;
     }
+    const int64_t n_cover = n_ep == 0 ? 0 : (n_scan_known >= 0 ? n_scan_known : n_total);
     char *base = static_cast<char *>(workspace);
     ScanArgs a;
     a.rew = rew, a.val = val, a.offsets = offsets, a.last_vals = last_vals;
-    a.n_scan = n_scan, a.n_ep = n_ep;
+    a.n_ep = n_ep;
     a.gamma = gamma, a.gl = gamma * lam;  // the reference forms gamma * lam in double (replay_buffer.py:70)
     a.adv = adv, a.ret = ret;
     a.ticket = reinterpret_cast<int *>(base + w.ticket);
@@ -527,19 +527,19 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
     a.agg = reinterpret_cast<Map *>(base + w.agg);
     a.incl = reinterpret_cast<double2 *>(base + w.incl);
     a.partials = reinterpret_cast<double2 *>(base + w.partials);
-    a.num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
-    if (a.num_tiles > 0) {
+    const int grid = (int)((n_cover + SCAN_TILE - 1) / SCAN_TILE);
+    if (grid > 0) {
         // ticket + flags must start at zero
         RRL_CUDA_OK(cudaMemsetAsync(base, 0, w.agg, stream), err);
         if (with_baseline)
-            scan_kernel<true><<<a.num_tiles, SCAN_THREADS, 0, stream>>>(a);
+            scan_kernel<true><<<grid, SCAN_THREADS, 0, stream>>>(a);
         else
-            scan_kernel<false><<<a.num_tiles, SCAN_THREADS, 0, stream>>>(a);
+            scan_kernel<false><<<grid, SCAN_THREADS, 0, stream>>>(a);
         RRL_CUDA_OK(cudaGetLastError(), err);
         if (launches) *launches += 1;
     }
     if (stats_out) {
-        stats_reduce_kernel<<<1, 1024, 0, stream>>>(a.partials, a.num_tiles, adv, n_scan, n_total, stats_out,
+        stats_reduce_kernel<<<1, 1024, 0, stream>>>(a.partials, offsets, n_ep, adv, n_total, stats_out,
                                                     finalize_stats_flag ? 1 : 0);
         RRL_CUDA_OK(cudaGetLastError(), err);
         if (launches) *launches += 1;

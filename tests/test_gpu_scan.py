@@ -201,8 +201,9 @@ def test_stateless_scan_device_large_properties():
         out = torch.empty(n, device=dev)
         normalise_device(adv, n, stats, out)
         torch.cuda.synchronize()
-        ref = (adv - np.float32(st[3])) / np.float32(st[4])
-        assert torch.equal(out, ref)
+        # numpy on the host divides in IEEE f32, as the reference does (replay_buffer.py:105)
+        ref = (adv.cpu().numpy() - np.float32(st[3])) / np.float32(st[4])
+        assert np.array_equal(out.cpu().numpy(), ref)
     # linearity (no baseline): scan(a*x) == a*scan(x) for a power of two, exactly
     adv2, ret2 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
     scan_device(d_rew * 4, d_val, d_offs, d_lvs, n, E, g, l, False, adv2, ret2, None, ws)
