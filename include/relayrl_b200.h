@@ -191,6 +191,25 @@ int32_t rrl_scan_device(const float *rew, const float *val, const int64_t *offse
                         const float *last_vals, int64_t n_total, int64_t n_ep, double gamma,
                         double lam, int32_t with_baseline, float *adv, float *ret,
                         double *stats_out, void *workspace, size_t workspace_bytes, void *stream);
+/* Same operator for callers that cannot allocate device memory (no counterpart in the reference:
+ * its learner never touches a GPU).  Meant for hosts whose device-memory budget is fixed at
+ * start-up -- a locked memory pool, a quota with no head-room, a plug-in inside an application
+ * that forbids allocation calls after initialisation -- and which therefore cannot supply the
+ * workspace rrl_scan_device wants.  The look-back descriptors live in a 557 312-byte array
+ * compiled into the library (resident on every GPU that loads it, until the process exits), so
+ * n_total is limited to RRL_SCAN_NOALLOC_MAX transitions; larger calls fail with RRL_EINVAL.
+ * The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine.
+ * The first call on each device resolves the array's device address (cudaGetSymbolAddress, with
+ * the caller's current device): make that first call before starting any stream capture.
+ * All calls on a device share the one array: two calls that overlap on the GPU (different
+ * streams, or different threads) race on it -- serialise them.  The array keeps the previous
+ * call's contents; the part that must start at zero is cleared on `stream` by every call.
+ * Arguments and results are exactly those of rrl_scan_device, minus the workspace. */
+#define RRL_SCAN_NOALLOC_MAX (16ll * 1024 * 1024)
+int32_t rrl_scan_device_noalloc(const float *rew, const float *val, const int64_t *offsets,
+                                const float *last_vals, int64_t n_total, int64_t n_ep, double gamma,
+                                double lam, int32_t with_baseline, float *adv, float *ret,
+                                double *stats_out, void *stream);
 /* out[i] = (adv[i] - mean) / std in f32, mean/std read from stats (device, as written above). */
 int32_t rrl_normalise_device(const float *adv, int64_t n, const double *stats, float *out, void *stream);
 

@@ -588,3 +588,87 @@ int32_t cvt_f64_f32_launch(const double *src, float *dst, int64_t n, cudaStream_
 }
 
 }  // namespace rrl
+
+// ---------------------------------------------------------------------------------------------
+// Scan entry point for callers that must not allocate device memory.
+//
+// Who needs it: hosts that own a fixed device-memory budget handed to them at start-up -- a
+// real-time trajectory server whose memory pool is carved out once and then locked, a process
+// running under a quota that leaves no room for a second cudaMalloc, or a plug-in loaded into
+// somebody else's CUDA context where the embedding application forbids allocation calls after
+// initialisation.  rrl_scan_device() asks such callers for a workspace they cannot produce.
+//
+// Here the tile descriptors of the single-pass look-back live in a fixed array that is part of
+// the library image: every GPU that loads librelayrl_b200.so carries these 557 312 bytes until
+// the process exits.  That bounds the size: at most RRL_SCAN_NOALLOC_MAX transitions per call.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace rrl {
+extern thread_local ErrBuf g_create_err;
+
+namespace {
+constexpr int64_t NOALLOC_MAX_TILES = RRL_SCAN_NOALLOC_MAX / SCAN_TILE;  // 8192
+// ticket (256) + flags + aggregates + inclusive values + statistic partials, each 256-aligned
+constexpr size_t NOALLOC_WS_BYTES = 256 + NOALLOC_MAX_TILES * (sizeof(int) + sizeof(Map) + 2 * sizeof(double2));
+static_assert(RRL_SCAN_NOALLOC_MAX % SCAN_TILE == 0, "limit must be a whole number of tiles");
+static_assert(NOALLOC_WS_BYTES == 557312, "documented size of the static scratch");
+
+static __device__ __align__(256) unsigned char g_scan_scratch[NOALLOC_WS_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of g_scan_scratch, per device ordinal
+}  // namespace
+}  // namespace rrl
+
+extern "C" int32_t rrl_scan_device_noalloc(const float *rew, const float *val, const int64_t *offsets,
+                                           const float *last_vals, int64_t n_total, int64_t n_ep, double gamma,
+                                           double lam, int32_t with_baseline, float *adv, float *ret,
+                                           double *stats_out, void *stream)
+{
+    using namespace rrl;
+    ErrBuf &err = g_create_err;
+    if (!rew || !adv || !ret || (with_baseline && !val) || (n_ep > 0 && (!offsets || !last_vals))) {
+        err.set("rrl_scan_device_noalloc: null pointer");
+        return RRL_EINVAL;
+    }
+    if (n_total < 0 || n_total > RRL_SCAN_NOALLOC_MAX) {
+        err.set("rrl_scan_device_noalloc: n_total = %lld exceeds the static scratch limit of %lld transitions; "
+                "use rrl_scan_device with a caller-provided workspace",
+                (long long)n_total, (long long)RRL_SCAN_NOALLOC_MAX);
+        return RRL_EINVAL;
+    }
+    if (scan_workspace_bytes(n_total) > NOALLOC_WS_BYTES) {
+        err.set("rrl_scan_device_noalloc: internal layout needs %zu bytes > %zu", scan_workspace_bytes(n_total),
+                (size_t)NOALLOC_WS_BYTES);
+        return RRL_EINVAL;
+    }
+    int dev = -1;
+    RRL_CUDA_OK(cudaGetDevice(&dev), err);
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+        err.set("rrl_scan_device_noalloc: device ordinal %d outside [0, %d)", dev, NOALLOC_MAX_DEVICES);
+        return RRL_EINVAL;
+    }
+    void *scratch = nullptr;
+    {
+        // Set-up, once per device, with that device current: in host code `g_scan_scratch` is only
+        // a stand-in symbol, not an address a kernel may dereference; the device address comes from
+        // cudaGetSymbolAddress.
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev]) {
+            void *p = nullptr;
+            RRL_CUDA_OK(cudaGetSymbolAddress(&p, g_scan_scratch), err);
+            if (!p) {
+                err.set("rrl_scan_device_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
+                return RRL_ECUDA;
+            }
+            g_noalloc_ptr[dev] = p;
+        }
+        scratch = g_noalloc_ptr[dev];
+    }
+    // scan_launch zeroes the ticket and the tile flags (the part that must start at zero) on `stream`
+    // before the kernel; everything else in the scratch is written before it is read.
+    return scan_launch(rew, val, offsets, last_vals, n_total, n_ep, gamma, lam, with_baseline != 0, adv, ret,
+                       stats_out, scratch, NOALLOC_WS_BYTES, true, -1, static_cast<cudaStream_t>(stream), err, nullptr);
+}

@@ -82,6 +82,8 @@ SIGNATURES = {
     "rrl_scan_workspace_bytes": (C.c_int32, [C.c_int64, C.POINTER(C.c_size_t)]),
     "rrl_scan_device": (C.c_int32, [_P, _P, _P, _P, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int32,
                                     _P, _P, _P, _P, C.c_size_t, _P]),
+    "rrl_scan_device_noalloc": (C.c_int32, [_P, _P, _P, _P, C.c_int64, C.c_int64, C.c_double, C.c_double,
+                                            C.c_int32, _P, _P, _P, _P]),
     "rrl_normalise_device": (C.c_int32, [_P, C.c_int64, _P, _P, _P]),
 }
 

@@ -258,6 +258,21 @@ def scan_device(rew, val, offsets, last_vals, n_total, n_ep, gamma, lam, with_ba
                                      C.c_void_p(stream) if stream else None))
 
 
+SCAN_NOALLOC_MAX = 16 * 1024 * 1024
+
+
+def scan_device_noalloc(rew, val, offsets, last_vals, n_total, n_ep, gamma, lam, with_baseline, adv, ret, stats,
+                        stream=None):
+    """rrl_scan_device_noalloc: the scan for hosts that may not allocate device memory (a locked
+    memory pool, an exhausted quota, a plug-in inside an application that bans allocation after
+    start-up).  Its scratch is a fixed array inside the library, hence n_total <= SCAN_NOALLOC_MAX;
+    calls on one device must not overlap; make the first call per device outside stream capture."""
+    check(_lib.lib().rrl_scan_device_noalloc(_dev_ptr(rew), _dev_ptr(val), _dev_ptr(offsets), _dev_ptr(last_vals),
+                                             n_total, n_ep, float(gamma), float(lam), int(with_baseline),
+                                             _dev_ptr(adv), _dev_ptr(ret), _dev_ptr(stats),
+                                             C.c_void_p(stream) if stream else None))
+
+
 def scan_workspace_bytes(n):
     b = C.c_size_t()
     check(_lib.lib().rrl_scan_workspace_bytes(n, C.byref(b)))
