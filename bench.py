@@ -5,9 +5,9 @@ A step is ONE full learner epoch on one batch of synthetic trajectories:
   ingest -> reward-to-go/GAE scan + statistics -> policy step -> train_vf_iters value steps
 (REINFORCE.receive_trajectory + train_model, reference REINFORCE.py:70-125).
 Workload (config.workload): REINFORCE with baseline, d=4, A=2, H=128, 80 value iterations, C3-style
-variable episode lengths, N = --n transitions per GPU (default 64 Mi = BASELINE's target batch).
+variable episode lengths, N = --transitions per GPU (default 64 Mi = BASELINE's target batch).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--n N_PER_GPU] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--transitions N_PER_GPU] [--impl reference]
 Under torchrun (N > 1) every rank owns its own shard (weak scaling); gradients/statistics are
 all-reduced over NCCL inside the library.  One JSON line is printed by rank 0.
 """
@@ -182,6 +182,49 @@ def workload_config(args, n):
             "parallelism": "dp%d" % args.gpus}
 
 
+def measure_scan(cols, offsets, last_vals, n, dev, with_baseline=True, reps=20):
+    """K2 alone: median CUDA-event time of rrl_scan_device on the stream it is launched on
+    (torch's current stream).  Inputs (0.5 GB at 64 Mi) exceed the 126 MB L2."""
+    import torch
+    from relayrl_b200 import scan_device, scan_workspace_bytes
+    ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    adv, ret = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    sstats = torch.zeros(8, dtype=torch.float64, device=dev)
+    d_off, d_lv = torch.from_numpy(offsets).to(dev), torch.from_numpy(last_vals).to(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
+    for i in range(3 + reps):
+        if i >= 3:
+            e0[i - 3].record()
+        scan_device(cols["rew"], cols["val"], d_off, d_lv, n, len(last_vals), GAMMA, LAM, with_baseline, adv, ret,
+                    sstats, ws, stream=stream)
+        if i >= 3:
+            e1[i - 3].record()
+    torch.cuda.synchronize()
+    return sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
+
+
+def run_scan_only(args):
+    import torch
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    n = args.n
+    rng = np.random.default_rng(64)
+    lens = episode_lengths(rng, n)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    cols = {"rew": torch.empty(n, device=dev).uniform_(-1, 1), "val": torch.randn(n, device=dev)}
+    last_vals = rng.uniform(-1, 1, len(lens)).astype(np.float32)
+    hbm, _, _, which = peaks()
+    out = {}
+    for wb, bpt in ((True, 16), (False, 12)):
+        ms = measure_scan(cols, offsets, last_vals, n, dev, with_baseline=wb)
+        gbs = bpt * n / (ms * 1e-3) / 1e9
+        out["with_baseline" if wb else "without_baseline"] = {"launch_ms": ms, "achieved": gbs, "unit": "GB/s",
+                                                              "peak": hbm, "frac": gbs / hbm, "bytes_per_transition": bpt}
+    print(json.dumps({"scan_only": out, "n": n, "episodes": int(len(lens)), "peak_source": which}))
+
+
 def run_ours(args):
     import torch
     from relayrl_b200 import Learner, _lib, nccl_unique_id, scan_device, scan_workspace_bytes
@@ -252,25 +295,7 @@ def run_ours(args):
     dt_e2e, stats_e2e = timed(step_e2e, max(1, min(args.steps, 2)), 1)
     e2e_steps = max(1, min(args.steps, 2))
 
-    # the scan alone, CUDA events on the stream it is launched on (torch's current stream)
-    ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
-    adv, ret = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
-    sstats = torch.zeros(8, dtype=torch.float64, device=dev)
-    d_off, d_lv = torch.from_numpy(offsets).to(dev), torch.from_numpy(last_vals).to(dev)
-    stream = torch.cuda.current_stream().cuda_stream
-    reps = 10
-    e0 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
-    e1 = [torch.cuda.Event(enable_timing=True) for _ in range(reps)]
-    for i in range(3 + reps):
-        if i >= 3:
-            e0[i - 3].record()
-        scan_device(cols["rew"], cols["val"], d_off, d_lv, n, len(last_vals), GAMMA, LAM, True, adv, ret, sstats, ws,
-                    stream=stream)
-        if i >= 3:
-            e1[i - 3].record()
-    torch.cuda.synchronize()
-    scan_ms = sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
-
+    scan_ms = measure_scan(cols, offsets, last_vals, n, dev)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -319,12 +344,15 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=1 << 26, help="transitions per GPU")
+    ap.add_argument("--transitions", dest="n", type=int, default=1 << 26, help="transitions per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=1 << 17)
     ap.add_argument("--ref-sample", type=int, default=1 << 17)
+    ap.add_argument("--scan-only", action="store_true", help="measure K2 alone (roofline_scan) and exit")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.scan_only:
+        run_scan_only(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -203,7 +203,7 @@ int32_t rrl_scan_device(const float *rew, const float *val, const int64_t *offse
  * the caller's current device): make that first call before starting any stream capture.
  * All calls on a device share the one array: two calls that overlap on the GPU (different
  * streams, or different threads) race on it -- serialise them.  The array keeps the previous
- * call's contents; the part that must start at zero is cleared on `stream` by every call.
+ * call's contents; the part that must start from a known state is reset on `stream` by every call.
  * Arguments and results are exactly those of rrl_scan_device, minus the workspace. */
 #define RRL_SCAN_NOALLOC_MAX (16ll * 1024 * 1024)
 int32_t rrl_scan_device_noalloc(const float *rew, const float *val, const int64_t *offsets,

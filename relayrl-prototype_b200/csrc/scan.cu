@@ -13,11 +13,13 @@
 // Algorithm: both recurrences y[t] = x[t] + c*y[t+1] are affine maps of the value carried in
 // from the right; maps compose associatively, and an episode end resets the carry (the map's
 // slope becomes 0).  One pass over HBM (16 B/transition with baseline, 12 B without):
-//   tile (2048 transitions/CTA, tiles handed out right-to-left by an atomic ticket)
-//     -> coalesced 128-bit loads into swizzled shared memory, blocked 8-per-thread reads
+//   persistent CTAs (cooperative launch), 2048-transition tiles taken right-to-left in a fixed
+//   stride; a producer warp prefetches the next tile while 8 consumer warps scan the current one
+//     -> cp.async 16-byte copies into swizzled shared memory, blocked 8-per-thread reads
 //     -> episode ends of the tile found by a 32-ary warp search in `offsets`
 //     -> thread-serial map, warp-shuffle suffix scan, 8 warp maps through shared memory
-//     -> single-pass decoupled look-back across tiles (aggregate / inclusive descriptors)
+//     -> single-pass decoupled look-back across tiles (aggregate / inclusive descriptors whose
+//        64-bit words carry their own validity: no flags, no fences on the critical path)
 //     -> second thread-serial pass seeded with the carry, results staged through shared
 //        memory and written with coalesced 128-bit stores
 //     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64.
@@ -28,7 +30,13 @@ namespace rrl {
 
 namespace {
 
-constexpr int SCAN_THREADS = 256;
+#ifndef SCAN_CONSUMER_THREADS
+#define SCAN_CONSUMER_THREADS 256
+#endif
+#ifndef SCAN_MIN_CTAS
+#define SCAN_MIN_CTAS 2
+#endif
+constexpr int SCAN_THREADS = SCAN_CONSUMER_THREADS;
 constexpr int SCAN_VPT = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VPT;  // 2048 transitions per CTA
 constexpr int SCAN_WARPS = SCAN_THREADS / 32;
@@ -80,15 +88,52 @@ __device__ __forceinline__ Map shfl_map(const Map &m, int src)
     return o;
 }
 
-__device__ __forceinline__ int ld_acquire(const int *p)
+// Tile descriptors carry their own validity: every 64-bit word starts as the sentinel 0xFFFF...F
+// (memset before the launch) and is written once with a single 64-bit store.  A reader polls the
+// words themselves (L2-coherent relaxed loads) -- no flag, no fence, no MEMBAR on the critical path.
+// The sentinel is a NaN payload the arithmetic here cannot produce.
+__device__ __forceinline__ bool is_unset(double x) { return __double_as_longlong(x) == -1ll; }
+__device__ __forceinline__ double2 ld_relaxed2(const double2 *p)
 {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    double2 v;
+    asm volatile("ld.relaxed.gpu.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release(int *p, int v)
+__device__ __forceinline__ void st_relaxed2(double2 *p, double x, double y)
 {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(x), "d"(y) : "memory");
+}
+
+// f32 <-> f64 by bit manipulation: the hardware conversion instructions (F2F.F64.F32 and back) issue
+// on the quarter-rate XU pipe, which the first version of this kernel saturated (95 % busy at 19 % of
+// HBM peak, profiles/r1_summary.md).  Zero, denormal, Inf and NaN take the slow instruction.
+// out of line on purpose: inlined, the compiler if-converts the rare branch and issues the slow
+// conversion for every element
+__device__ __noinline__ double f32_to_f64_slow(float x) { return (double)x; }
+__device__ __noinline__ float f64_to_f32_slow(double d) { return __double2float_rn(d); }
+
+__device__ __forceinline__ double f32_to_f64(float x)
+{
+    const unsigned u = __float_as_uint(x);
+    const unsigned a = u & 0x7fffffffu;
+    if (a - 0x00800000u >= 0x7f000000u && a != 0u) return f32_to_f64_slow(x);  // denormal / Inf / NaN (rare)
+    const unsigned hi = (u & 0x80000000u) | ((a >> 3) + 0x38000000u);
+    return __hiloint2double(a ? hi : u, u << 29);
+}
+// d rounded to 24 significant bits, still a double (Veltkamp split with 2^29 + 1)
+__device__ __forceinline__ double round_to_f32_precision(double d)
+{
+    // explicit _rn intrinsics: the compiler must not contract c - d into an FMA
+    const double c = __dmul_rn(d, 536870913.0);
+    return __dsub_rn(c, __dsub_rn(c, d));
+}
+// h = round_to_f32_precision(d): exact narrowing by bits when h is a normal f32, else the slow instruction on d
+__device__ __forceinline__ float narrow_f32(double h, double d)
+{
+    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
+    const unsigned t = hi - 0x38000000u;             // exponent rebased from 1023 to 127 (sign untouched)
+    if (((t << 1) >> 21) - 1u >= 254u) return f64_to_f32_slow(d);  // zero, f32-denormal range, overflow, Inf, NaN
+    return __uint_as_float((hi & 0x80000000u) | __funnelshift_l(lo, t, 3));
 }
 
 struct ScanArgs {
@@ -97,95 +142,115 @@ struct ScanArgs {
     const float *last_vals;
     int64_t n_ep;    // closed paths; the scan covers [0, offsets[n_ep]) (read on the device)
     double gamma, gl;
+    double gamma_p, gl_p;  // gamma^SCAN_VPT, gl^SCAN_VPT: the slope of a thread's map when no path ends in its run
     float *adv, *ret;
     // workspace
     int *ticket;
-    int *flags;      // 0 = nothing, 1 = aggregate published, 2 = inclusive published
+    int *flags;      // (reserved)
     Map *agg;        // tile map (carry-in from the right -> value at the tile's first element)
     double2 *incl;   // final (ret, adv) at the tile's first element
     double2 *partials;
 };
 
 // tile states published for the look-back
-constexpr int FLAG_AGG = 1, FLAG_INCL = 2;
 
-template <bool WB>
-__global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
+// ---- persistent, warp-specialised tile pipeline ------------------------------------------------
+// A CTA is 8 consumer warps + 1 producer warp.  CTA c owns the logical tiles c, c+G, c+2G, ...
+// (logical tile j = physical tile num_tiles-1-j: right-most first); the launch is cooperative, so
+// all G CTAs are co-resident and the look-back can never wait on a CTA that is not running.
+// While the consumers work on tile j, the producer warp prepares tile j+G in the other buffer:
+// cp.async of rew/val into swizzled shared memory (the bytes in flight that keep HBM busy), the
+// 32-ary search for the tile's first path boundary, and the end-of-path bit mask + last_vals.
+constexpr int SCAN_CTA_THREADS = SCAN_THREADS + 32;
+
+struct TileBuf {
+    float r[SCAN_SMEM_FLOATS];   // rew in, adv out
+    float v[SCAN_SMEM_FLOATS];   // val in, ret out
+    float lv[SCAN_TILE];         // last_val at the positions where a path ends
+    unsigned end[SCAN_TILE / 32];
+    int tile;                    // physical tile index, -1 = no more work
+    int pad[3];
+};
+static_assert(sizeof(TileBuf) % 16 == 0, "TileBuf must keep 16-byte alignment");
+
+__device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gmem_src, int src_bytes)
 {
-    __shared__ __align__(16) float r_s[SCAN_SMEM_FLOATS];
-    __shared__ __align__(16) float v_s[SCAN_SMEM_FLOATS];
-    __shared__ float lv_s[SCAN_TILE];
-    __shared__ unsigned end_s[SCAN_TILE / 32];
-    __shared__ Map wm_s[SCAN_WARPS];
-    __shared__ double carry_s[2];
-    __shared__ double red_s[SCAN_WARPS][2];
-    __shared__ int tile_s;
-    __shared__ long long e0_s;
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(SCAN_THREADS) : "memory"); }
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t n_scan = a.offsets[a.n_ep];  // end of the last closed path
-    const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
-    if (tid == 0) tile_s = num_tiles - 1 - atomicAdd(a.ticket, 1);  // right-most tile first
-    if (tid < SCAN_TILE / 32) end_s[tid] = 0u;
-    __syncthreads();
-    const int tile = tile_s;
-    if (tile < 0) return;  // the grid is sized for n_total; CTAs beyond the scanned range have no work
+// producer warp: fill `B` for physical tile `tile` (or mark it empty)
+template <bool WB>
+__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan, int lane)
+{
+    if (lane == 0) B.tile = tile;
+    if (tile < 0) return;
+    for (int w = lane; w < SCAN_TILE / 32; w += 32) B.end[w] = 0u;
     const int64_t t0 = (int64_t)tile * SCAN_TILE;
     const int cnt = (int)min((int64_t)SCAN_TILE, n_scan - t0);
+    // 512 16-byte chunks per array, 16 per lane; out-of-range bytes are zero-filled
+#pragma unroll 4
+    for (int c = lane; c < SCAN_TILE / 4; c += 32) {
+        const int valid = min(max(cnt - 4 * c, 0), 4) * 4;
+        const int64_t g = valid ? t0 + 4 * c : 0;
+        cp_async16_zfill(&B.r[sidx(4 * c)], a.rew + g, valid);
+        if (WB) cp_async16_zfill(&B.v[sidx(4 * c)], a.val + g, valid);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (WB && lane == 0) B.v[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
 
-    // ---- coalesced loads into swizzled shared memory ---------------------------------------
-#pragma unroll
-    for (int c = tid; c < SCAN_TILE / 4; c += SCAN_THREADS) {
-        const int64_t g = t0 + 4 * c;
-        float4 r4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = r4;
-        if (g + 3 < n_scan) {
-            r4 = __ldcs(reinterpret_cast<const float4 *>(a.rew + g));
-            if (WB) v4 = __ldcs(reinterpret_cast<const float4 *>(a.val + g));
+    // first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0
+    long long lo = 1, hi = a.n_ep;
+    while (lo < hi) {
+        const long long span = hi - lo;
+        const long long p = lo + (span * (lane + 1)) / 33;
+        const bool gt = a.offsets[p] > t0;
+        const unsigned b = __ballot_sync(0xffffffffu, gt);
+        if (b == 0u) {
+            lo = lo + (span * 32) / 33 + 1;
         } else {
-            float *rp = &r4.x, *vp = &v4.x;
-            for (int k = 0; k < 4; ++k)
-                if (g + k < n_scan) {
-                    rp[k] = a.rew[g + k];
-                    if (WB) vp[k] = a.val[g + k];
+            const int f = __ffs(b) - 1;
+            hi = lo + (span * (f + 1)) / 33;
+            if (f > 0) lo = lo + (span * f) / 33 + 1;
+        }
+    }
+    __syncwarp();  // the zeroed mask words are visible to the whole warp before the atomics
+    const int64_t t1 = t0 + cnt;
+    for (long long k0 = lo; k0 <= a.n_ep; k0 += 128) {
+        // four independent probes per lane per round keep the dependent-load count low when
+        // paths are very short
+        bool more = false;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long k = k0 + u * 32 + lane;
+            if (k <= a.n_ep) {
+                const int64_t b = a.offsets[k];
+                if (b <= t1) {
+                    if (u == 3) more = true;
+                    if (b > a.offsets[k - 1]) {  // a non-empty path ends at b-1
+                        const int pos = (int)(b - 1 - t0);
+                        atomicOr(&B.end[pos >> 5], 1u << (pos & 31));
+                        B.lv[pos] = a.last_vals[k - 1];
+                    }
                 }
+            }
         }
-        *reinterpret_cast<float4 *>(&r_s[sidx(4 * c)]) = r4;
-        if (WB) *reinterpret_cast<float4 *>(&v_s[sidx(4 * c)]) = v4;
+        if (!__any_sync(0xffffffffu, more)) break;  // offsets are sorted: nothing further can fall in the tile
     }
-    if (WB && tid == 0) v_s[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+}
 
-    // ---- first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0 ------------
-    if (warp == 0) {
-        long long lo = 1, hi = a.n_ep;
-        while (lo < hi) {
-            const long long span = hi - lo;
-            const long long p = lo + (span * (lane + 1)) / 33;
-            const bool gt = a.offsets[p] > t0;
-            const unsigned b = __ballot_sync(0xffffffffu, gt);
-            if (b == 0u) {
-                lo = lo + (span * 32) / 33 + 1;
-            } else {
-                const int f = __ffs(b) - 1;
-                hi = lo + (span * (f + 1)) / 33;
-                if (f > 0) lo = lo + (span * f) / 33 + 1;
-            }
-        }
-        if (lane == 0) e0_s = lo;
-    }
-    __syncthreads();
-    {
-        const int64_t t1 = t0 + cnt;
-        for (long long k = e0_s + tid; k <= a.n_ep; k += SCAN_THREADS) {
-            const int64_t b = a.offsets[k];
-            if (b > t1) break;
-            if (b > a.offsets[k - 1]) {  // a non-empty path ends at b-1
-                const int pos = (int)(b - 1 - t0);
-                atomicOr(&end_s[pos >> 5], 1u << (pos & 31));
-                lv_s[pos] = a.last_vals[k - 1];
-            }
-        }
-    }
-    __syncthreads();
+// consumer warps (threads 0..255): scan the tile in `B`, publish / look back, write the outputs
+template <bool WB>
+__device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan,
+                                             int num_tiles, Map *wm_s, double *carry_s, double (*red_s)[2],
+                                             int tid)
+{
+    const int lane = tid & 31, warp = tid >> 5;
+    float *r_s = B.r, *v_s = B.v;
+    const int64_t t0 = (int64_t)tile * SCAN_TILE;
+    const int cnt = (int)min((int64_t)SCAN_TILE, n_scan - t0);
 
     // ---- blocked reads: SCAN_VPT consecutive transitions per thread ---------------------------
     const int j0 = tid * SCAN_VPT;
@@ -201,34 +266,56 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         }
     }
     const float v_edge = WB ? v_s[sidx(j0 + SCAN_VPT)] : 0.f;
-    const unsigned eb = (end_s[j0 >> 5] >> (j0 & 31)) & 0xffu;
-    const bool open_right = ((end_s[(cnt - 1) >> 5] >> ((cnt - 1) & 31)) & 1u) == 0u;
+    const unsigned eb = (B.end[j0 >> 5] >> (j0 & 31)) & 0xffu;
+    const bool open_right = ((B.end[(cnt - 1) >> 5] >> ((cnt - 1) & 31)) & 1u) == 0u;
 
-    // ---- pass 1: this thread's map ------------------------------------------------------------
+    // ---- pass 1: this thread's map; inputs are widened once and kept (rr = reward, dl = the
+    // GAE delta, both pure data) so that pass 2 is two DFMAs per transition ----------------------
     Map m;
+    double rr[SCAN_VPT], dl[WB ? SCAN_VPT : 1];
     {
-        double ret_n = 0.0, adv_n = 0.0, v_n = (double)v_edge, ar = 1.0, aa = 1.0;
+        double ret_n = 0.0, adv_n = 0.0, v_n = WB ? f32_to_f64(v_edge) : 0.0;
+        if (eb == 0u) {  // no path ends inside this thread's run (the common case)
 #pragma unroll
-        for (int k = SCAN_VPT - 1; k >= 0; --k) {
-            if ((eb >> k) & 1u) {
-                // with baseline the marker's reward bootstraps both recurrences
-                // (replay_buffer.py:66-73); without it is ignored (replay_buffer.py:75-77)
-                const double lvk = (double)lv_s[j0 + k];
-                ret_n = WB ? lvk : 0.0;
-                adv_n = 0.0;
-                v_n = lvk;
-                ar = 0.0;
-                aa = 0.0;
+            for (int k = SCAN_VPT - 1; k >= 0; --k) {
+                rr[k] = f32_to_f64(r[k]);
+                if (WB) {
+                    const double vk = f32_to_f64(v[k]);
+                    dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
+                    v_n = vk;
+                }
+                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
+                ret_n = fma(a.gamma, ret_n, rr[k]);
             }
-            const double rr = (double)r[k];
-            const double delta = WB ? (fma(a.gamma, v_n, rr) - (double)v[k]) : rr;
-            adv_n = fma(a.gl, adv_n, delta);
-            ret_n = fma(a.gamma, ret_n, rr);
-            ar *= a.gamma;
-            aa *= a.gl;
-            if (WB) v_n = (double)v[k];
+            m.ar = a.gamma_p, m.aa = a.gl_p;
+        } else {
+            double ar = 1.0, aa = 1.0;
+#pragma unroll
+            for (int k = SCAN_VPT - 1; k >= 0; --k) {
+                if ((eb >> k) & 1u) {
+                    // with baseline the marker's reward bootstraps both recurrences
+                    // (replay_buffer.py:66-73); without it is ignored (replay_buffer.py:75-77)
+                    const double lvk = f32_to_f64(B.lv[j0 + k]);
+                    ret_n = WB ? lvk : 0.0;
+                    adv_n = 0.0;
+                    v_n = lvk;
+                    ar = 0.0;
+                    aa = 0.0;
+                }
+                rr[k] = f32_to_f64(r[k]);
+                if (WB) {
+                    const double vk = f32_to_f64(v[k]);
+                    dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
+                    v_n = vk;
+                }
+                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
+                ret_n = fma(a.gamma, ret_n, rr[k]);
+                ar *= a.gamma;
+                aa *= a.gl;
+            }
+            m.ar = ar, m.aa = aa;
         }
-        m.ar = ar, m.br = ret_n, m.aa = aa, m.ba = adv_n;
+        m.br = ret_n, m.ba = adv_n;
     }
 
     // ---- warp suffix scan of the maps (lane l: M_l∘M_{l+1}∘...∘M_31) ----------------------------
@@ -241,7 +328,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
     Map Ex = shfl_down_map(S, 1);  // maps of the lanes to the right of this one
     if (lane == 31) Ex.ar = 1.0, Ex.br = 0.0, Ex.aa = 1.0, Ex.ba = 0.0;
     if (lane == 0) wm_s[warp] = S;
-    __syncthreads();  // (also: every thread has finished reading r_s / v_s)
+    consumer_sync();  // (also: every consumer has finished reading r_s / v_s)
 
     Map Wsuf;  // maps of the warps to the right of this one
     Wsuf.ar = 1.0, Wsuf.br = 0.0, Wsuf.aa = 1.0, Wsuf.ba = 0.0;
@@ -253,11 +340,11 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         const bool closed = (T.ar == 0.0 && T.aa == 0.0);  // value at the tile's first element is final
         if (lane == 0) {
             if (closed) {
-                a.incl[tile] = make_double2(T.br, T.ba);
-                st_release(&a.flags[tile], FLAG_INCL);
+                st_relaxed2(&a.incl[tile], T.br, T.ba);
             } else {
-                a.agg[tile] = T;
-                st_release(&a.flags[tile], FLAG_AGG);
+                double2 *ap = reinterpret_cast<double2 *>(&a.agg[tile]);
+                st_relaxed2(ap, T.ar, T.br);
+                st_relaxed2(ap + 1, T.aa, T.ba);
             }
         }
         double cr = 0.0, ca = 0.0;
@@ -270,17 +357,18 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
                 Map q;
                 q.ar = 0.0, q.br = 0.0, q.aa = 0.0, q.ba = 0.0;
                 if (k < num_tiles) {
-                    int f;
-                    do {
-                        f = ld_acquire(&a.flags[k]);
-                    } while (f == 0);
-                    if (f == FLAG_INCL) {
-                        const double2 iv = __ldcg(&a.incl[k]);
-                        q.br = iv.x, q.ba = iv.y;
-                    } else {
-                        const double2 *ap = reinterpret_cast<const double2 *>(&a.agg[k]);
-                        const double2 lo2 = __ldcg(ap), hi2 = __ldcg(ap + 1);
-                        q.ar = lo2.x, q.br = lo2.y, q.aa = hi2.x, q.ba = hi2.y;
+                    const double2 *ap = reinterpret_cast<const double2 *>(&a.agg[k]);
+                    while (true) {
+                        const double2 iv = ld_relaxed2(&a.incl[k]);
+                        if (!is_unset(iv.x) && !is_unset(iv.y)) {  // final value of that tile's first element
+                            q.br = iv.x, q.ba = iv.y;
+                            break;
+                        }
+                        const double2 lo2 = ld_relaxed2(ap), hi2 = ld_relaxed2(ap + 1);
+                        if (!is_unset(lo2.x) && !is_unset(lo2.y) && !is_unset(hi2.x) && !is_unset(hi2.y)) {
+                            q.ar = lo2.x, q.br = lo2.y, q.aa = hi2.x, q.ba = hi2.y;
+                            break;
+                        }
                     }
                 }
                 __syncwarp();
@@ -303,38 +391,31 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
             }
         }
         if (lane == 0) {
-            if (!closed) {
-                a.incl[tile] = make_double2(fma(T.ar, cr, T.br), fma(T.aa, ca, T.ba));
-                st_release(&a.flags[tile], FLAG_INCL);
-            }
+            if (!closed) st_relaxed2(&a.incl[tile], fma(T.ar, cr, T.br), fma(T.aa, ca, T.ba));
             carry_s[0] = cr, carry_s[1] = ca;
         }
     }
-    __syncthreads();
+    consumer_sync();
 
     // ---- pass 2: final values, seeded with the carry ------------------------------------------
     double s1 = 0.0, s2 = 0.0;
     {
         const double wr = fma(Wsuf.ar, carry_s[0], Wsuf.br), wa = fma(Wsuf.aa, carry_s[1], Wsuf.ba);
-        double ret_n = fma(Ex.ar, wr, Ex.br), adv_n = fma(Ex.aa, wa, Ex.ba), v_n = (double)v_edge;
+        double ret_n = fma(Ex.ar, wr, Ex.br), adv_n = fma(Ex.aa, wa, Ex.ba);
         float ao[SCAN_VPT], ro[SCAN_VPT];
 #pragma unroll
         for (int k = SCAN_VPT - 1; k >= 0; --k) {
-            if ((eb >> k) & 1u) {
-                const double lvk = (double)lv_s[j0 + k];
-                ret_n = WB ? lvk : 0.0;
+            if (eb != 0u && ((eb >> k) & 1u)) {
+                ret_n = WB ? f32_to_f64(B.lv[j0 + k]) : 0.0;
                 adv_n = 0.0;
-                v_n = lvk;
             }
-            const double rr = (double)r[k];
-            const double delta = WB ? (fma(a.gamma, v_n, rr) - (double)v[k]) : rr;
-            adv_n = fma(a.gl, adv_n, delta);
-            ret_n = fma(a.gamma, ret_n, rr);
-            if (WB) v_n = (double)v[k];
-            ao[k] = (float)adv_n;
-            ro[k] = (float)ret_n;
+            adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
+            ret_n = fma(a.gamma, ret_n, rr[k]);
+            const double ha = round_to_f32_precision(adv_n);
+            ao[k] = narrow_f32(ha, adv_n);
+            ro[k] = narrow_f32(round_to_f32_precision(ret_n), ret_n);
             if (j0 + k < cnt) {
-                const double x = (double)ao[k];
+                const double x = f32_to_f64(ao[k]);  // the f32-rounded advantage, as the reference's buffer holds it
                 s1 += x;
                 s2 = fma(x, x, s2);
             }
@@ -350,7 +431,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         s2 += __shfl_xor_sync(0xffffffffu, s2, d);
     }
     if (lane == 0) red_s[warp][0] = s1, red_s[warp][1] = s2;
-    __syncthreads();
+    consumer_sync();
 
     // ---- coalesced 128-bit stores -------------------------------------------------------------
 #pragma unroll
@@ -374,6 +455,40 @@ __global__ void __launch_bounds__(SCAN_THREADS, 3) scan_kernel(ScanArgs a)
         double t1 = 0.0, t2 = 0.0;
         for (int w = 0; w < SCAN_WARPS; ++w) t1 += red_s[w][0], t2 += red_s[w][1];
         a.partials[tile] = make_double2(t1, t2);
+    }
+}
+
+template <bool WB>
+__global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(ScanArgs a)
+{
+    extern __shared__ __align__(16) unsigned char scan_dyn[];
+    TileBuf *buf = reinterpret_cast<TileBuf *>(scan_dyn);
+    __shared__ Map wm_s[SCAN_WARPS];
+    __shared__ double carry_s[2];
+    __shared__ double red_s[SCAN_WARPS][2];
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool producer = tid >= SCAN_THREADS;
+    const int64_t n_scan = a.offsets[a.n_ep];  // end of the last closed path
+    const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
+    const int G = gridDim.x;
+    int j = blockIdx.x;  // logical tile; physical = num_tiles - 1 - j (right-most first)
+
+    if (producer) scan_prepare<WB>(a, buf[0], j < num_tiles ? num_tiles - 1 - j : -1, n_scan, lane);
+    __syncthreads();
+    int b = 0;
+    while (true) {
+        const int tile = buf[b].tile;
+        if (tile < 0) break;
+        if (producer) {
+            const int jn = j + G;
+            scan_prepare<WB>(a, buf[b ^ 1], jn < num_tiles ? num_tiles - 1 - jn : -1, n_scan, lane);
+        } else {
+            scan_consume<WB>(a, buf[b], tile, n_scan, num_tiles, wm_s, carry_s, red_s, tid);
+        }
+        __syncthreads();
+        b ^= 1;
+        j += G;
     }
 }
 
@@ -521,21 +636,34 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
     a.rew = rew, a.val = val, a.offsets = offsets, a.last_vals = last_vals;
     a.n_ep = n_ep;
     a.gamma = gamma, a.gl = gamma * lam;  // the reference forms gamma * lam in double (replay_buffer.py:70)
+    a.gamma_p = 1.0, a.gl_p = 1.0;
+    for (int i = 0; i < SCAN_VPT; ++i) a.gamma_p *= a.gamma, a.gl_p *= a.gl;  // same products the serial path forms
     a.adv = adv, a.ret = ret;
     a.ticket = reinterpret_cast<int *>(base + w.ticket);
     a.flags = reinterpret_cast<int *>(base + w.flags);
     a.agg = reinterpret_cast<Map *>(base + w.agg);
     a.incl = reinterpret_cast<double2 *>(base + w.incl);
     a.partials = reinterpret_cast<double2 *>(base + w.partials);
-    const int grid = (int)((n_cover + SCAN_TILE - 1) / SCAN_TILE);
-    if (grid > 0) {
-        // ticket + flags must start at zero
-        RRL_CUDA_OK(cudaMemsetAsync(base, 0, w.agg, stream), err);
-        if (with_baseline)
-            scan_kernel<true><<<grid, SCAN_THREADS, 0, stream>>>(a);
-        else
-            scan_kernel<false><<<grid, SCAN_THREADS, 0, stream>>>(a);
-        RRL_CUDA_OK(cudaGetLastError(), err);
+    const int tiles = (int)((n_cover + SCAN_TILE - 1) / SCAN_TILE);
+    if (tiles > 0) {
+        // every descriptor word starts as the "unset" sentinel
+        RRL_CUDA_OK(cudaMemsetAsync(base + w.agg, 0xFF, w.partials - w.agg, stream), err);
+        const size_t smem = 2 * sizeof(TileBuf);
+        const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
+                                       : reinterpret_cast<const void *>(scan_kernel<false>);
+        RRL_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
+        int dev = 0, sms = 0, per_sm = 0;
+        RRL_CUDA_OK(cudaGetDevice(&dev), err);
+        RRL_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), err);
+        RRL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SCAN_CTA_THREADS, smem), err);
+        if (per_sm < 1) {
+            err.set("scan: kernel does not fit on an SM (%zu B shared memory)", smem);
+            return RRL_ECUDA;
+        }
+        // co-resident by construction: the look-back spins on tiles owned by other CTAs
+        const int grid = std::min(tiles, per_sm * sms);
+        void *args[] = {&a};
+        RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SCAN_CTA_THREADS), args, smem, stream), err);
         if (launches) *launches += 1;
     }
     if (stats_out) {
@@ -612,7 +740,9 @@ constexpr int64_t NOALLOC_MAX_TILES = RRL_SCAN_NOALLOC_MAX / SCAN_TILE;  // 8192
 // ticket (256) + flags + aggregates + inclusive values + statistic partials, each 256-aligned
 constexpr size_t NOALLOC_WS_BYTES = 256 + NOALLOC_MAX_TILES * (sizeof(int) + sizeof(Map) + 2 * sizeof(double2));
 static_assert(RRL_SCAN_NOALLOC_MAX % SCAN_TILE == 0, "limit must be a whole number of tiles");
+#if SCAN_CONSUMER_THREADS == 256
 static_assert(NOALLOC_WS_BYTES == 557312, "documented size of the static scratch");
+#endif
 
 static __device__ __align__(256) unsigned char g_scan_scratch[NOALLOC_WS_BYTES];
 
@@ -667,8 +797,8 @@ extern "C" int32_t rrl_scan_device_noalloc(const float *rew, const float *val, c
         }
         scratch = g_noalloc_ptr[dev];
     }
-    // scan_launch zeroes the ticket and the tile flags (the part that must start at zero) on `stream`
-    // before the kernel; everything else in the scratch is written before it is read.
+    // scan_launch resets the tile descriptors (the only part of the scratch that is read before it
+    // is written) on `stream` before the kernel.
     return scan_launch(rew, val, offsets, last_vals, n_total, n_ep, gamma, lam, with_baseline != 0, adv, ret,
                        stats_out, scratch, NOALLOC_WS_BYTES, true, -1, static_cast<cudaStream_t>(stream), err, nullptr);
 }

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "librelayrl_b200.so")
+SO_PATH = os.environ.get("RELAYRL_B200_SO") or os.path.join(_HERE, "librelayrl_b200.so")
 
 RRL_OK = 0
 RRL_F32, RRL_F64 = 0, 1
