@@ -1,0 +1,161 @@
+// tcgen05 (5th-generation tensor core) building blocks for sm_100a: TMEM allocation, UMMA shared-memory
+// and instruction descriptors, MMA issue/commit, TMEM loads, and the bf16x3 operand split that gives
+// fp32-accurate products on the bf16 tensor pipe.  Inline PTX; no CUTLASS.
+//
+// Operand storage ("X layout"): a matrix X[row][feature] (R rows, F features, bf16) is stored as
+//     byte offset(row, feature) = (feature / 8) * (R * 16) + row * 16 + (feature % 8) * 2
+// i.e. for every 8-feature chunk, all rows' 16-byte pieces are contiguous.  This is the canonical
+// un-swizzled UMMA layout in BOTH orientations, so one copy serves as
+//   * a K-major operand   (M/N = row,     K = feature): LBO = R*16 (next K chunk), SBO = 128 (next 8 rows)
+//   * an MN-major operand (M/N = feature, K = row):     SBO = R*16 (next MN chunk), LBO = 128 (next 8 K)
+// (core matrix = 8 x 16 B = 128 contiguous bytes in either view).
+//
+// fp32 accuracy from bf16 tensor cores: a = a1 + a2 + a3 with each part a bf16 (8+8+8 mantissa bits),
+// a*b ~= a1b1 + (a1b2 + a2b1) + (a1b3 + a2b2 + a3b1): six MMAs accumulated in fp32 in TMEM; the
+// dropped terms are below 2^-24 |a||b|.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rrl {
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- X layout ---------------------------------------------------------------------------------
+__device__ __forceinline__ int x_off_bytes(int row, int feature, int R) { return (feature >> 3) * (R * 16) + row * 16 + (feature & 7) * 2; }
+
+// ---- bf16x3 split -------------------------------------------------------------------------------
+struct Split3 {
+    __nv_bfloat16 p1, p2, p3;
+};
+__device__ __forceinline__ Split3 split3(float a)
+{
+    Split3 s;
+    s.p1 = __float2bfloat16_rn(a);
+    const float r1 = a - __bfloat162float(s.p1);  // exact
+    s.p2 = __float2bfloat16_rn(r1);
+    const float r2 = r1 - __bfloat162float(s.p2);  // exact
+    s.p3 = __float2bfloat16_rn(r2);
+    return s;
+}
+
+// ---- descriptors -----------------------------------------------------------------------------------
+// shared-memory matrix descriptor, SWIZZLE_NONE, Blackwell version field = 1
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((addr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+// instruction descriptor for kind::f16 with bf16 inputs and fp32 accumulation
+__host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, bool a_mn_major, bool b_mn_major)
+{
+    return (1u << 4)                       // c_format = F32
+           | (1u << 7)                     // a_format = BF16
+           | (1u << 10)                    // b_format = BF16
+           | ((a_mn_major ? 1u : 0u) << 15)
+           | ((b_mn_major ? 1u : 0u) << 16)
+           | ((uint32_t)(N >> 3) << 17)
+           | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- TMEM ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t *smem_dst, uint32_t ncols)  // one full warp
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols)  // the same warp
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// generic-proxy smem writes -> visible to the tensor core (async proxy)
+__device__ __forceinline__ void fence_smem_to_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread
+__device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+        : "memory");
+}
+// all previously issued MMAs of this thread -> arrive on the mbarrier when they have completed
+__device__ __forceinline__ void mma_commit(uint64_t *bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// ---- mbarrier -----------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// ---- TMEM -> registers: 32 lanes x 32 consecutive 32-bit columns (thread = lane) -------------------------
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// The six bf16x3 products of one GEMM, smallest terms first.  Plane p (0,1,2) of an operand starts at
+// base + p * plane_bytes; per K step (16 elements of K) the start address advances by a_kstep / b_kstep.
+struct OperandDesc {
+    uint32_t base, plane_bytes, lbo, sbo, kstep;
+};
+__device__ __forceinline__ void issue_gemm_bf16x3(uint32_t d_tmem, const OperandDesc &A, const OperandDesc &B, uint32_t idesc,
+                                                  int ksteps, bool accumulate_into_d)
+{
+    const int pa[6] = {0, 1, 2, 0, 1, 0}, pb[6] = {2, 1, 0, 1, 0, 0};
+    bool acc = accumulate_into_d;
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+        const uint32_t a0 = A.base + pa[t] * A.plane_bytes, b0 = B.base + pb[t] * B.plane_bytes;
+        for (int s = 0; s < ksteps; ++s) {
+            mma_bf16(d_tmem, smem_desc(a0 + s * A.kstep, A.lbo, A.sbo), smem_desc(b0 + s * B.kstep, B.lbo, B.sbo), idesc, acc);
+            acc = true;
+        }
+    }
+}
+
+}  // namespace tc
+}  // namespace rrl

@@ -1,0 +1,103 @@
+// Self-test of the tcgen05 building blocks (tc_common.cuh): one CTA computes one bf16x3 GEMM in each
+// of the three operand orientations the fused learner kernel uses.  Exported for tests only
+// (tests/test_gpu_tc.py); not part of include/relayrl_b200.h.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace rrl {
+namespace {
+
+using namespace tc;
+
+// mode 0: D[128 x 64]  = A[128 x 128] * B[64 x 128]^T      (A K-major, B K-major)     -- forward GEMM
+// mode 1: D[128 x 64]  = A[128 x 128]^T * B[64 x 128]^T    (A MN-major, B K-major)    -- data-gradient GEMM
+// mode 2: D[128 x 128] = A[64 x 128]^T * B[64 x 128]       (A MN-major, B MN-major)   -- weight-gradient GEMM
+// All inputs row-major fp32 [rows][128] in global memory.
+__global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const float *__restrict__ A,
+                                                              const float *__restrict__ B, float *__restrict__ D)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int RA = mode == 2 ? 64 : 128, RB = 64;
+    const uint32_t planeA = RA * 128 * 2, planeB = RB * 128 * 2;
+    unsigned char *sa = smem, *sb = smem + 3 * planeA;
+
+    for (int i = tid; i < RA * 128; i += 128) {
+        const int r = i >> 7, f = i & 127;
+        const Split3 s = split3(A[i]);
+        const int o = x_off_bytes(r, f, RA);
+        *reinterpret_cast<__nv_bfloat16 *>(sa + o) = s.p1;
+        *reinterpret_cast<__nv_bfloat16 *>(sa + planeA + o) = s.p2;
+        *reinterpret_cast<__nv_bfloat16 *>(sa + 2 * planeA + o) = s.p3;
+    }
+    for (int i = tid; i < RB * 128; i += 128) {
+        const int r = i >> 7, f = i & 127;
+        const Split3 s = split3(B[i]);
+        const int o = x_off_bytes(r, f, RB);
+        *reinterpret_cast<__nv_bfloat16 *>(sb + o) = s.p1;
+        *reinterpret_cast<__nv_bfloat16 *>(sb + planeB + o) = s.p2;
+        *reinterpret_cast<__nv_bfloat16 *>(sb + 2 * planeB + o) = s.p3;
+    }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 128);
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    fence_smem_to_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_base_s;
+
+    const int N = mode == 2 ? 128 : 64;
+    if (tid == 0) {
+        OperandDesc a, b;
+        a.base = smem_u32(sa), a.plane_bytes = planeA;
+        b.base = smem_u32(sb), b.plane_bytes = planeB;
+        int ksteps;
+        uint32_t idesc;
+        if (mode == 0) {  // K = features
+            a.lbo = RA * 16, a.sbo = 128, a.kstep = 2 * RA * 16;
+            b.lbo = RB * 16, b.sbo = 128, b.kstep = 2 * RB * 16;
+            ksteps = 8, idesc = idesc_bf16(128, 64, false, false);
+        } else if (mode == 1) {  // A: M = features, K = rows(128); B: K = features
+            a.sbo = RA * 16, a.lbo = 128, a.kstep = 2 * 128;
+            b.lbo = RB * 16, b.sbo = 128, b.kstep = 2 * RB * 16;
+            ksteps = 8, idesc = idesc_bf16(128, 64, true, false);
+        } else {  // both: M/N = features, K = rows(64)
+            a.sbo = RA * 16, a.lbo = 128, a.kstep = 2 * 128;
+            b.sbo = RB * 16, b.lbo = 128, b.kstep = 2 * 128;
+            ksteps = 4, idesc = idesc_bf16(128, 128, true, true);
+        }
+        issue_gemm_bf16x3(tmem, a, b, idesc, ksteps, false);
+        mma_commit(&bar);
+    }
+    mbar_wait(&bar, 0);
+    fence_after_sync();
+
+    // epilogue: warp w owns TMEM lanes 32w..32w+31 (= rows of D)
+    for (int c0 = 0; c0 < N; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + c0, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) D[(size_t)tid * N + c0 + i] = v[i];
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+}  // namespace
+}  // namespace rrl
+
+extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *B, float *D, void *stream)
+{
+    using namespace rrl;
+    if (mode < 0 || mode > 2 || !A || !B || !D) return RRL_EINVAL;
+    const size_t smem = 3 * (size_t)(mode == 2 ? 64 : 128) * 128 * 2 + 3 * 64 * 128 * 2;
+    if (cudaFuncSetAttribute(tc_gemm_test_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
+    tc_gemm_test_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(mode, A, B, D);
+    return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;
+}
