@@ -16,33 +16,13 @@
 // gradient that NCCL all-reduces and Adam consumes.
 //
 // This file is the fp32 CUDA-core implementation of the three HxH GEMMs per tile.
-#include "common.cuh"
+#include "mlp_internal.cuh"
+
+#include <stdlib.h>
 
 namespace rrl {
 
 namespace {
-
-constexpr int MLP_THREADS = 256;
-constexpr int TILE_M = 64;       // transitions per tile
-constexpr int FLUSH_TILES = 16;  // f32 accumulation window (1024 transitions) before the f64 spill
-constexpr int MAX_OUT = 32;      // act_dim limit of the fused head
-constexpr int HEAD_ACC = MAX_OUT / 4;
-
-enum { MODE_VALUE = 0, MODE_POLICY_REF = 1, MODE_POLICY_LSM = 2 };
-
-struct MlpArgs {
-    const float *params;  // flat torch order
-    int d, out;
-    const float *obs, *act, *mask, *adv, *ret, *logp_old;
-    const double *stats;  // AdvStats
-    int64_t n;            // local transitions
-    float inv_n;          // 1 / N_global as torch's mean-backward forms it (f32)
-    double *partials;     // [grid][P] float64 gradient partials
-    double *loss_partials;  // [grid][4]
-    int64_t n_params;
-    // optional forward taps (eval): per-row outputs
-    float *out_rows;  // MODE_VALUE: v[n]; policy: logits [n][out]
-};
 
 struct SmemLayout {
     int dpad, dp, ldh, S;
@@ -603,7 +583,10 @@ int32_t run_pass(NetState &net, const TrainBuffers &tb, int mode, bool with_grad
     int grid = (int)std::min<int64_t>(net.grid, std::max<int64_t>(tiles, 1));
     const size_t smem = mlp_smem_bytes(nd.d, nd.H, nd.out);
     int32_t st;
-    if (mode == MODE_VALUE)
+    static const bool tc_off = getenv("RRL_DISABLE_TC") != nullptr;
+    if (!tc_off && tc_pass_supported(nd, mode, with_grad))
+        st = tc_pass_launch(a, nd, mode, grid, stream, err);
+    else if (mode == MODE_VALUE)
         st = launch_h<MODE_VALUE>(net, a, with_grad, grid, smem, stream, err);
     else if (mode == MODE_POLICY_REF)
         st = launch_h<MODE_POLICY_REF>(net, a, with_grad, grid, smem, stream, err);

