@@ -26,9 +26,13 @@ using namespace tc;
 constexpr int TC_H = 128;
 constexpr int TC_MAX_D = 8;
 constexpr int TC_MAX_OUT = 4;
-constexpr int W_PLANE = TC_H * TC_H * 2;    // bytes of one bf16 plane of W2
-constexpr int X_PLANE = TILE_M * TC_H * 2;  // bytes of one bf16 plane of a 64-row activation tile
+constexpr int W_PLANE = tc::x_plane_bytes(TC_H, TC_H);    // bytes of one bf16 plane of W2
+constexpr int X_PLANE = tc::x_plane_bytes(TILE_M, TC_H);  // bytes of one bf16 plane of a 64-row activation tile
+constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H), X_CHUNK = tc::x_chunk_bytes(TILE_M);
 constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_COLS = 256;
+constexpr int TC_THREADS = 512;            // 16 warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
+constexpr int TC_RG = TC_THREADS / 128;    // row groups per tile
+constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (16)
 
 // shared-memory map (bytes)
 constexpr int OFF_W2 = 0;
@@ -44,21 +48,18 @@ constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters
 constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;  // f32 [64][4]
 constexpr int OFF_ROWF = OFF_MASK + TILE_M * TC_MAX_OUT * 4;  // f32 tgt, lpo, g, valid [64] each
 constexpr int OFF_ACT = OFF_ROWF + 4 * TILE_M * 4;            // int [64]
-constexpr int OFF_RED = OFF_ACT + TILE_M * 4;                 // double [8]
-constexpr int OFF_BAR = OFF_RED + 64;                         // 2 mbarriers + tmem base
+constexpr int OFF_RED = OFF_ACT + TILE_M * 4;                 // double [16]
+constexpr int OFF_BAR = OFF_RED + 128;                         // 2 mbarriers + tmem base
 constexpr int TC_SMEM_BYTES = OFF_BAR + 32;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
 
-__device__ __forceinline__ uint32_t pack2(__nv_bfloat16 lo, __nv_bfloat16 hi)
-{
-    return (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
-}
-
-// sum over the 32 lanes of p[c] for every c; lane l returns the total for c == l
-__device__ __forceinline__ float reduce_scatter32(float (&p)[32], int lane)
+// 16 values per lane: lane l returns the total over the 32 lanes for c == (l & 15)
+__device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
 {
 #pragma unroll
-    for (int w = 16; w >= 1; w >>= 1) {
+    for (int i = 0; i < 16; ++i) p[i] += __shfl_xor_sync(0xffffffffu, p[i], 16);
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1) {
         const bool upper = (lane & w) != 0;
 #pragma unroll
         for (int i = 0; i < w; ++i) {
@@ -71,7 +72,7 @@ __device__ __forceinline__ float reduce_scatter32(float (&p)[32], int lane)
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
+__global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char *w2_p = smem + OFF_W2, *h1_p = smem + OFF_H1, *dz_p = smem + OFF_DZ;
@@ -83,11 +84,11 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
           *valid_s = tgt_s + 3 * TILE_M;
     int *act_s = reinterpret_cast<int *>(smem + OFF_ACT);
     double *red_s = reinterpret_cast<double *>(smem + OFF_RED);
-    uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1;
-    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar2 + 1);
+    uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1, *bar3 = bar1 + 2;
+    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar3 + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int q = warp & 3, hh = warp >> 2;  // TMEM lane quarter of this warp, which half of the 64 rows
+    const int q = warp & 3, rq = warp >> 2;  // TMEM lane quarter of this warp, which group of 16 rows
     const int j = 32 * q + lane;             // the hidden unit this thread owns in both epilogues
     const int d = a.d, out = a.out;
     const NetDims nd{d, TC_H, out};
@@ -95,24 +96,25 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     // ---- one-time set-up: weights -> shared memory (W2 as three bf16 planes), TMEM, mbarriers ------
     {
         const float *W1 = a.params + nd.oW1(), *W2 = a.params + nd.oW2(), *W3 = a.params + nd.oW3();
-        for (int i = tid; i < TC_H * TC_H; i += MLP_THREADS) {
-            const Split3 s = split3(W2[i]);
+        for (int i = tid; i < TC_H * TC_H; i += TC_THREADS) {
+            const Trunc3 s = trunc3(W2[i]);
             const int o = x_off_bytes(i >> 7, i & 127, TC_H);  // row = out unit, feature = in unit
-            *reinterpret_cast<__nv_bfloat16 *>(w2_p + o) = s.p1;
-            *reinterpret_cast<__nv_bfloat16 *>(w2_p + W_PLANE + o) = s.p2;
-            *reinterpret_cast<__nv_bfloat16 *>(w2_p + 2 * W_PLANE + o) = s.p3;
+            *reinterpret_cast<unsigned short *>(w2_p + o) = hi16(s.t1);
+            *reinterpret_cast<unsigned short *>(w2_p + W_PLANE + o) = hi16(s.t2);
+            *reinterpret_cast<unsigned short *>(w2_p + 2 * W_PLANE + o) = hi16(s.t3);
         }
-        for (int i = tid; i < TC_H * TC_MAX_D; i += MLP_THREADS) {
+        for (int i = tid; i < TC_H * TC_MAX_D; i += TC_THREADS) {
             const int u = i / TC_MAX_D, c = i - u * TC_MAX_D;
             w1_s[i] = c < d ? W1[u * d + c] : 0.f;
         }
-        for (int i = tid; i < TC_MAX_OUT * TC_H; i += MLP_THREADS) w3_s[i] = i < out * TC_H ? W3[i] : 0.f;
+        for (int i = tid; i < TC_MAX_OUT * TC_H; i += TC_THREADS) w3_s[i] = i < out * TC_H ? W3[i] : 0.f;
         if (tid < TC_H) b1_s[tid] = a.params[nd.ob1() + tid], b2_s[tid] = a.params[nd.ob2() + tid];
         if (tid < TC_MAX_OUT) b3_s[tid] = tid < out ? a.params[nd.ob3() + tid] : 0.f;
         if (warp == 0) tmem_alloc(tmem_s, TM_COLS);
         if (tid == 0) {
             mbar_init(bar1, 1);
             mbar_init(bar2, 1);
+            mbar_init(bar3, 1);
             mbar_fence_init();
         }
     }
@@ -129,23 +131,23 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     // operand descriptors (tc_common.cuh: K-major -> LBO = R*16, SBO = 128; MN-major -> SBO = R*16, LBO = 128)
     OperandDesc W2_k, W2_mn, H1_k, H1_mn, DZ_k, DZ_mn;
     W2_k.base = W2_mn.base = smem_u32(w2_p), W2_k.plane_bytes = W2_mn.plane_bytes = W_PLANE;
-    W2_k.lbo = TC_H * 16, W2_k.sbo = 128, W2_k.kstep = 2 * TC_H * 16;
-    W2_mn.sbo = TC_H * 16, W2_mn.lbo = 128, W2_mn.kstep = 256;
+    W2_k.lbo = W_CHUNK, W2_k.sbo = 128, W2_k.kstep = 2 * W_CHUNK;
+    W2_mn.sbo = W_CHUNK, W2_mn.lbo = 128, W2_mn.kstep = 256;
     H1_k.base = H1_mn.base = smem_u32(h1_p), H1_k.plane_bytes = H1_mn.plane_bytes = X_PLANE;
-    H1_k.lbo = TILE_M * 16, H1_k.sbo = 128, H1_k.kstep = 2 * TILE_M * 16;
-    H1_mn.sbo = TILE_M * 16, H1_mn.lbo = 128, H1_mn.kstep = 256;
+    H1_k.lbo = X_CHUNK, H1_k.sbo = 128, H1_k.kstep = 2 * X_CHUNK;
+    H1_mn.sbo = X_CHUNK, H1_mn.lbo = 128, H1_mn.kstep = 256;
     DZ_k = H1_k, DZ_mn = H1_mn;
     DZ_k.base = DZ_mn.base = smem_u32(dz_p);
     constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, false),
                        ID_G3 = idesc_bf16(128, 128, true, true);
 
     // thread-local gradient accumulators for hidden unit j over this thread's half of the rows
-    // dW2 row j, this warp's 64 in-units: drained from TMEM after every tile.  The tensor core adds into
+    // dW2 row j, this warp's 32 in-units: drained from TMEM after every tile.  The tensor core adds into
     // its fp32 accumulator with truncation (measured bias -4e-8 per MMA), so letting dW2 ride in TMEM
     // across tiles cost ~4e-6 of accuracy after 8 tiles; 24 MMAs per drain keep it at the CUDA-core level.
-    float dW2sum[64];
+    float dW2sum[32];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) dW2sum[i] = 0.f;
+    for (int i = 0; i < 32; ++i) dW2sum[i] = 0.f;
     float dW3acc[TC_MAX_OUT], dW1acc[TC_MAX_D], db1acc = 0.f, db2acc = 0.f, db3acc[TC_MAX_OUT];
 #pragma unroll
     for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
@@ -163,12 +165,12 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         const int rows = (int)min((int64_t)TILE_M, a.n - row0);
 
         // ---- P0: tile inputs ----------------------------------------------------------------------
-        for (int i = tid; i < TILE_M * TC_MAX_D; i += MLP_THREADS) {
+        for (int i = tid; i < TILE_M * TC_MAX_D; i += TC_THREADS) {
             const int m = i / TC_MAX_D, c = i - m * TC_MAX_D;
             obs_s[i] = (m < rows && c < d) ? __ldcs(a.obs + (row0 + m) * d + c) : 0.f;
         }
         if (MODE != MODE_VALUE)
-            for (int i = tid; i < TILE_M * TC_MAX_OUT; i += MLP_THREADS) {
+            for (int i = tid; i < TILE_M * TC_MAX_OUT; i += TC_THREADS) {
                 const int m = i / TC_MAX_OUT, c = i - m * TC_MAX_OUT;
                 mask_s[i] = (m < rows && c < out) ? __ldcs(a.mask + (row0 + m) * out + c) : 1.f;
             }
@@ -189,7 +191,7 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 
         // ---- P1: H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) ----
 #pragma unroll 1
-        for (int it = tid; it < TILE_M * (TC_H / 8); it += MLP_THREADS) {
+        for (int it = tid; it < TILE_M * (TC_H / 8); it += TC_THREADS) {
             const int r = it & (TILE_M - 1), ch = it >> 6;
             float4 x[TC_MAX_D / 4];
 #pragma unroll
@@ -198,7 +200,7 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             uint32_t w1[4], w2[4], w3[4];
 #pragma unroll
             for (int e = 0; e < 8; e += 2) {
-                Split3 s[2];
+                Trunc3 s[2];
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
                     const int u = 8 * ch + e + t;
@@ -210,11 +212,11 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                             acc = fmaf(x[i4].x, w.x, acc), acc = fmaf(x[i4].y, w.y, acc);
                             acc = fmaf(x[i4].z, w.z, acc), acc = fmaf(x[i4].w, w.w, acc);
                         }
-                    s[t] = split3(fmaxf(acc, 0.f));
+                    s[t] = trunc3(fmaxf(acc, 0.f));
                 }
-                w1[e >> 1] = pack2(s[0].p1, s[1].p1), w2[e >> 1] = pack2(s[0].p2, s[1].p2), w3[e >> 1] = pack2(s[0].p3, s[1].p3);
+                w1[e >> 1] = pack_hi16(s[0].t1, s[1].t1), w2[e >> 1] = pack_hi16(s[0].t2, s[1].t2), w3[e >> 1] = pack_hi16(s[0].t3, s[1].t3);
             }
-            const int o = ch * (TILE_M * 16) + r * 16;
+            const int o = ch * X_CHUNK + r * 16;
             *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
             *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
             *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(w3[0], w3[1], w3[2], w3[3]);
@@ -232,20 +234,20 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         mbar_wait(bar1, parity);
         fence_after_sync();
 
-        // ---- P3: epilogue 1 (thread = hidden unit j, rows 32*hh .. 32*hh+31) ---------------------------
-        float h2[32];
+        // ---- P3: epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) ---------------------------
+        float h2[TC_RPT];
         {
-            tmem_ld32(tmem_lane + TM_D1 + 32 * hh, h2);
+            tmem_ld16(tmem_lane + TM_D1 + TC_RPT * rq, h2);
             const float b2 = b2_s[j];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) h2[c] = fmaxf(h2[c] + b2, 0.f);
+            for (int c = 0; c < TC_RPT; ++c) h2[c] = fmaxf(h2[c] + b2, 0.f);
             for (int o_ = 0; o_ < out; ++o_) {
                 const float w3 = w3_s[o_ * TC_H + j];
-                float p[32];
+                float p[TC_RPT];
 #pragma unroll
-                for (int c = 0; c < 32; ++c) p[c] = h2[c] * w3;
-                const float tot = reduce_scatter32(p, lane);  // row 32*hh + lane, summed over this warp's 32 units
-                vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + 32 * hh + lane] = tot;
+                for (int c = 0; c < TC_RPT; ++c) p[c] = h2[c] * w3;
+                const float tot = reduce_scatter16(p, lane);  // row 16*rq + (lane & 15), summed over this warp's 32 units
+                if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
         }
         __syncthreads();
@@ -300,8 +302,8 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         {  // dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2
             float dbl = 0.f;
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-                const int m = 32 * hh + c;
+            for (int c = 0; c < TC_RPT; ++c) {
+                const int m = TC_RPT * rq + c;
                 const float g = g_s[m];
                 const int at = act_s[m];
                 const float dz = h2[c] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
@@ -309,11 +311,11 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
                 for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
                 dbl += dz;
-                const Split3 s = split3(dz);
+                const Trunc3 s = trunc3(dz);
                 const int o = x_off_bytes(m, j, TILE_M);
-                *reinterpret_cast<__nv_bfloat16 *>(dz_p + o) = s.p1;
-                *reinterpret_cast<__nv_bfloat16 *>(dz_p + X_PLANE + o) = s.p2;
-                *reinterpret_cast<__nv_bfloat16 *>(dz_p + 2 * X_PLANE + o) = s.p3;
+                *reinterpret_cast<unsigned short *>(dz_p + o) = hi16(s.t1);
+                *reinterpret_cast<unsigned short *>(dz_p + X_PLANE + o) = hi16(s.t2);
+                *reinterpret_cast<unsigned short *>(dz_p + 2 * X_PLANE + o) = hi16(s.t3);
             }
             db2acc += dbl;
         }
@@ -324,23 +326,25 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         // ---- P4: G3 (dW2 accumulates in TMEM) and G2 -------------------------------------------------------
         if (tid == 0) {
             fence_after_sync();
-            issue_gemm_bf16x3(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, TILE_M / 16, false);
+            // G2 first: epilogue 2 only needs D2 and runs while the tensor core is still busy with G3
             issue_gemm_bf16x3(tmem + TM_D2, W2_mn, DZ_k, ID_G2, TC_H / 16, false);
             mma_commit(bar2);
+            issue_gemm_bf16x3(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, TILE_M / 16, false);
+            mma_commit(bar3);
         }
         mbar_wait(bar2, parity);
         fence_after_sync();
 
         // ---- P5: epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
         {
-            float dh[32];
-            tmem_ld32(tmem_lane + TM_D2 + 32 * hh, dh);
+            float dh[TC_RPT];
+            tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
             float dbl = 0.f;
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-                const int m = 32 * hh + c;
+            for (int c = 0; c < TC_RPT; ++c) {
+                const int m = TC_RPT * rq + c;
                 const unsigned short hb = *reinterpret_cast<const unsigned short *>(h1_p + x_off_bytes(m, j, TILE_M));
-                // h1 >= 0 after the ReLU; its leading bf16 part is zero iff h1 is (h1 < 2^-134 aside)
+                // h1 >= 0 after the ReLU; its leading bf16 part is zero iff h1 is (h1 < 2^-126 aside)
                 const float dz1 = (hb & 0x7fffu) != 0 ? dh[c] : 0.f;
                 dbl += dz1;
 #pragma unroll
@@ -356,13 +360,14 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             }
             db1acc += dbl;
         }
-        // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's half of the in units) ----------------
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
+        // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's quarter of the in units) -------------
+        mbar_wait(bar3, parity);
+        fence_after_sync();
+        {
             float v[32];
-            tmem_ld32(tmem_lane + TM_DW2 + 64 * hh + 32 * half, v);
+            tmem_ld32(tmem_lane + TM_DW2 + 32 * rq, v);
 #pragma unroll
-            for (int c = 0; c < 32; ++c) dW2sum[32 * half + c] += v[c];
+            for (int c = 0; c < 32; ++c) dW2sum[c] += v[c];
         }
 
         // ---- spill the f32 window into the CTA's float64 partials -------------------------------------------
@@ -376,31 +381,53 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 else
                     my_partials[p] += (double)v;
             };
+            // dW2 (128 x 128 f32) is transposed through shared memory (the H1 and dz planes are idle:
+            // 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
+            float *w2stage = reinterpret_cast<float *>(h1_p);  // [128][129]
+            __syncthreads();  // every warp has finished epilogue 2, which still reads the H1 planes
 #pragma unroll
-            for (int c = 0; c < 64; ++c) {
-                put(nd.oW2() + (int64_t)j * TC_H + 64 * hh + c, dW2sum[c]);
+            for (int c = 0; c < 32; ++c) {
+                w2stage[j * 129 + 32 * rq + c] = dW2sum[c];
                 dW2sum[c] = 0.f;
             }
-            // per-unit accumulators: the two row-halves meet in shared memory (the dz planes are idle now)
-            float *stage = reinterpret_cast<float *>(dz_p);  // [2][128][S], S = 2 + MAX_OUT + MAX_D
+            __syncthreads();
+            {
+                double *dst = my_partials + nd.oW2();
+                double old[TC_H * TC_H / TC_THREADS];
+#pragma unroll
+                for (int e = 0; e < TC_H * TC_H / TC_THREADS; ++e) old[e] = first_flush ? 0.0 : __ldcg(dst + tid + e * TC_THREADS);
+#pragma unroll
+                for (int e = 0; e < TC_H * TC_H / TC_THREADS; ++e) {
+                    const int idx = tid + e * TC_THREADS;
+                    __stcg(dst + idx, old[e] + (double)w2stage[(idx >> 7) * 129 + (idx & 127)]);
+                }
+            }
+            __syncthreads();
+            // per-unit accumulators: the row groups meet in shared memory (the dz planes are idle now)
+            float *stage = reinterpret_cast<float *>(dz_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
             constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
-            float *mine = stage + (hh * TC_H + j) * S;
+            float *mine = stage + (rq * TC_H + j) * S;
             mine[0] = db1acc, mine[1] = db2acc;
 #pragma unroll
             for (int i = 0; i < TC_MAX_OUT; ++i) mine[2 + i] = dW3acc[i];
 #pragma unroll
             for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
-            float *stage3 = stage + 2 * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
+            float *stage3 = stage + TC_RG * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
             if (tid < TILE_M)
 #pragma unroll
                 for (int i = 0; i < TC_MAX_OUT; ++i) stage3[tid * TC_MAX_OUT + i] = db3acc[i];
             __syncthreads();
             if (tid < TC_H) {
-                const float *p0 = stage + tid * S, *p1 = stage + (TC_H + tid) * S;
-                put(nd.ob1() + tid, p0[0] + p1[0]);
-                put(nd.ob2() + tid, p0[1] + p1[1]);
-                for (int o_ = 0; o_ < out; ++o_) put(nd.oW3() + (int64_t)o_ * TC_H + tid, p0[2 + o_] + p1[2 + o_]);
-                for (int i = 0; i < d; ++i) put(nd.oW1() + (int64_t)tid * d + i, p0[2 + TC_MAX_OUT + i] + p1[2 + TC_MAX_OUT + i]);
+                auto tot = [&](int k) {
+                    float t = 0.f;
+#pragma unroll
+                    for (int g_ = 0; g_ < TC_RG; ++g_) t += stage[(g_ * TC_H + tid) * S + k];
+                    return t;
+                };
+                put(nd.ob1() + tid, tot(0));
+                put(nd.ob2() + tid, tot(1));
+                for (int o_ = 0; o_ < out; ++o_) put(nd.oW3() + (int64_t)o_ * TC_H + tid, tot(2 + o_));
+                for (int i = 0; i < d; ++i) put(nd.oW1() + (int64_t)tid * d + i, tot(2 + TC_MAX_OUT + i));
             }
             if (tid < out) {
                 float s = 0.f;
@@ -449,10 +476,10 @@ int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, 
     (void)nd;
     if (mode == MODE_VALUE) {
         RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_VALUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_VALUE><<<grid, MLP_THREADS, TC_SMEM_BYTES, stream>>>(a);
+        mlp_tc_kernel<MODE_VALUE><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(a);
     } else {
         RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_POLICY_REF>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_POLICY_REF><<<grid, MLP_THREADS, TC_SMEM_BYTES, stream>>>(a);
+        mlp_tc_kernel<MODE_POLICY_REF><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(a);
     }
     RRL_CUDA_OK(cudaGetLastError(), err);
     return RRL_OK;

@@ -3,11 +3,13 @@
 // fp32-accurate products on the bf16 tensor pipe.  Inline PTX; no CUTLASS.
 //
 // Operand storage ("X layout"): a matrix X[row][feature] (R rows, F features, bf16) is stored as
-//     byte offset(row, feature) = (feature / 8) * (R * 16) + row * 16 + (feature % 8) * 2
-// i.e. for every 8-feature chunk, all rows' 16-byte pieces are contiguous.  This is the canonical
-// un-swizzled UMMA layout in BOTH orientations, so one copy serves as
-//   * a K-major operand   (M/N = row,     K = feature): LBO = R*16 (next K chunk), SBO = 128 (next 8 rows)
-//   * an MN-major operand (M/N = feature, K = row):     SBO = R*16 (next MN chunk), LBO = 128 (next 8 K)
+//     byte offset(row, feature) = (feature / 8) * C + row * 16 + (feature % 8) * 2,   C = R * 16 + 16
+// i.e. for every 8-feature chunk, all rows' 16-byte pieces are contiguous; the 16 bytes of padding per
+// chunk rotate the shared-memory banks from chunk to chunk, so a warp that owns 32 features of one row
+// (the epilogues) stores and loads without bank conflicts.  This is the canonical un-swizzled UMMA
+// layout in BOTH orientations, so one copy serves as
+//   * a K-major operand   (M/N = row,     K = feature): LBO = C (next K chunk), SBO = 128 (next 8 rows)
+//   * an MN-major operand (M/N = feature, K = row):     SBO = C (next MN chunk), LBO = 128 (next 8 K)
 // (core matrix = 8 x 16 B = 128 contiguous bytes in either view).
 //
 // fp32 accuracy from bf16 tensor cores: a = a1 + a2 + a3 with each part a bf16 (8+8+8 mantissa bits),
@@ -24,7 +26,9 @@ namespace tc {
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ---- X layout ---------------------------------------------------------------------------------
-__device__ __forceinline__ int x_off_bytes(int row, int feature, int R) { return (feature >> 3) * (R * 16) + row * 16 + (feature & 7) * 2; }
+__host__ __device__ constexpr int x_chunk_bytes(int R) { return R * 16 + 16; }
+__host__ __device__ constexpr int x_plane_bytes(int R, int F) { return (F / 8) * x_chunk_bytes(R); }
+__device__ __forceinline__ int x_off_bytes(int row, int feature, int R) { return (feature >> 3) * x_chunk_bytes(R) + row * 16 + (feature & 7) * 2; }
 
 // ---- bf16x3 split -------------------------------------------------------------------------------
 struct Split3 {
@@ -40,6 +44,28 @@ __device__ __forceinline__ Split3 split3(float a)
     s.p3 = __float2bfloat16_rn(r2);
     return s;
 }
+
+// Truncating variant kept in fp32 containers: t1 + t2 + t3 == a up to 2^-24 |a|, each t_k has only its
+// top 16 bits set (so it IS a bf16 once the upper half-word is taken).  Two LOPs + two FADDs per
+// element; pairs are packed into bf16x2 words with one byte-permute per plane.
+struct Trunc3 {
+    float t1, t2, t3;
+};
+__device__ __forceinline__ Trunc3 trunc3(float a)
+{
+    Trunc3 s;
+    s.t1 = __uint_as_float(__float_as_uint(a) & 0xffff0000u);
+    const float r1 = a - s.t1;  // exact
+    s.t2 = __uint_as_float(__float_as_uint(r1) & 0xffff0000u);
+    s.t3 = r1 - s.t2;           // exact; its low half-word is dropped when packed
+    return s;
+}
+// bf16x2 word {lo = top half of x, hi = top half of y}
+__device__ __forceinline__ uint32_t pack_hi16(float x, float y) { return __byte_perm(__float_as_uint(x), __float_as_uint(y), 0x7632); }
+__device__ __forceinline__ unsigned short hi16(float x) { return (unsigned short)(__float_as_uint(x) >> 16); }
+
+// 32 lanes x 16 consecutive columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]);
 
 // ---- descriptors -----------------------------------------------------------------------------------
 // shared-memory matrix descriptor, SWIZZLE_NONE, Blackwell version field = 1
@@ -135,6 +161,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
+{
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
 // The six bf16x3 products of one GEMM, smallest terms first.  Plane p (0,1,2) of an operand starts at

@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int RA = mode == 2 ? 64 : 128, RB = 64;
-    const uint32_t planeA = RA * 128 * 2, planeB = RB * 128 * 2;
+    const uint32_t planeA = x_plane_bytes(RA, 128), planeB = x_plane_bytes(RB, 128);
     unsigned char *sa = smem, *sb = smem + 3 * planeA;
 
     for (int i = tid; i < RA * 128; i += 128) {
@@ -59,16 +59,16 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
         int ksteps;
         uint32_t idesc;
         if (mode == 0) {  // K = features
-            a.lbo = RA * 16, a.sbo = 128, a.kstep = 2 * RA * 16;
-            b.lbo = RB * 16, b.sbo = 128, b.kstep = 2 * RB * 16;
+            a.lbo = x_chunk_bytes(RA), a.sbo = 128, a.kstep = 2 * x_chunk_bytes(RA);
+            b.lbo = x_chunk_bytes(RB), b.sbo = 128, b.kstep = 2 * x_chunk_bytes(RB);
             ksteps = 8, idesc = idesc_bf16(128, 64, false, false);
         } else if (mode == 1) {  // A: M = features, K = rows(128); B: K = features
-            a.sbo = RA * 16, a.lbo = 128, a.kstep = 2 * 128;
-            b.lbo = RB * 16, b.sbo = 128, b.kstep = 2 * RB * 16;
+            a.sbo = x_chunk_bytes(RA), a.lbo = 128, a.kstep = 2 * 128;
+            b.lbo = x_chunk_bytes(RB), b.sbo = 128, b.kstep = 2 * x_chunk_bytes(RB);
             ksteps = 8, idesc = idesc_bf16(128, 64, true, false);
         } else {  // both: M/N = features, K = rows(64)
-            a.sbo = RA * 16, a.lbo = 128, a.kstep = 2 * 128;
-            b.sbo = RB * 16, b.lbo = 128, b.kstep = 2 * 128;
+            a.sbo = x_chunk_bytes(RA), a.lbo = 128, a.kstep = 2 * 128;
+            b.sbo = x_chunk_bytes(RB), b.lbo = 128, b.kstep = 2 * 128;
             ksteps = 4, idesc = idesc_bf16(128, 128, true, true);
         }
         issue_gemm_bf16x3(tmem, a, b, idesc, ksteps, false);
@@ -96,7 +96,7 @@ extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *
 {
     using namespace rrl;
     if (mode < 0 || mode > 2 || !A || !B || !D) return RRL_EINVAL;
-    const size_t smem = 3 * (size_t)(mode == 2 ? 64 : 128) * 128 * 2 + 3 * 64 * 128 * 2;
+    const size_t smem = 3 * (size_t)rrl::tc::x_plane_bytes(mode == 2 ? 64 : 128, 128) + 3 * (size_t)rrl::tc::x_plane_bytes(64, 128);
     if (cudaFuncSetAttribute(tc_gemm_test_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
     tc_gemm_test_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(mode, A, B, D);
     return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;
