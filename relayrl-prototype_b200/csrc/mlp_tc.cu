@@ -5,15 +5,19 @@
 //
 // Per tile (M = 64 transitions), with X[row][feature] operands in the un-swizzled "X layout"
 // (tc_common.cuh) as three bf16 planes each:
-//   H1  = relu(obs W1^T + b1)                       CUDA cores (K = obs_dim is tiny) -> planes
-//   D1^T[out x row] = W2 * H1^T                     G1: A = W2 (K-major),  B = H1 (K-major),  N = 64
-//   epilogue 1 (thread = hidden unit, 32 rows): h2 = relu(D1 + b2); head = W3 h2 (warp reduce-scatter);
+//   stage 1:  H1 = relu(obs W1^T + b1)               CUDA cores (K = obs_dim is tiny) -> planes + relu bit mask
+//   G1:       D1^T[out x row] = W2 * H1^T            A = W2 (K-major),  B = H1 (K-major),  N = 64
+//   epilogue 1 (thread = hidden unit, 16 rows): h2 = relu(D1 + b2); head = W3 h2 (warp reduce-scatter);
 //       loss, dhead per row; dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2 accumulate thread-locally
-//   dW2[out x in] += dZ2^T * H1                     G3: A = dZ2 (MN-major), B = H1 (MN-major), N = 128, K = 64 rows
-//   D2^T[in x row] = W2^T * dZ2^T                   G2: A = W2 (MN-major), B = dZ2 (K-major),  N = 64
+//   G3:       dW2[out x in] = dZ2^T * H1             A = dZ2 (MN-major), B = H1 (MN-major), N = 128, K = 64 rows
+//   G2:       D2^T[in x row] = W2^T * dZ2^T          A = W2 (MN-major), B = dZ2 (K-major),  N = 64
 //   epilogue 2 (thread = hidden unit): dz1 = D2 [h1 > 0]; dW1, db1 accumulate thread-locally
-// dW2 is drained from TMEM into per-thread f32 sums after every tile; every FLUSH_TILES tiles everything
-// spills into the CTA's float64 partials exactly like the CUDA-core kernel.
+// Schedule (the operand planes are single buffered -- W2 + H1 + dZ2 fill shared memory -- so the overlap
+// comes from the order of work): G3 goes first; as soon as it retires the H1 planes are free and stage 1 of
+// the NEXT tile runs under G2; G1 of the next tile is issued before epilogue 2 of this one and runs under it.
+// The tile inputs are fetched from global memory one tile ahead.  dW2 is drained from TMEM into per-thread
+// f32 sums after every tile; every FLUSH_TILES tiles everything spills into the CTA's float64 partials
+// exactly like the CUDA-core kernel.
 #include "mlp_internal.cuh"
 #include "tc_common.cuh"
 
@@ -38,20 +42,23 @@ constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (
 constexpr int OFF_W2 = 0;
 constexpr int OFF_H1 = OFF_W2 + 3 * W_PLANE;
 constexpr int OFF_DZ = OFF_H1 + 3 * X_PLANE;
-constexpr int OFF_OBS = OFF_DZ + 3 * X_PLANE;                 // f32 [64][16]
-constexpr int OFF_W1 = OFF_OBS + TILE_M * TC_MAX_D * 4;       // f32 [128][16]
+constexpr int OFF_OBS = OFF_DZ + 3 * X_PLANE;                 // f32 [2][64][8]
+constexpr int OFF_W1 = OFF_OBS + 2 * TILE_M * TC_MAX_D * 4;   // f32 [128][8]
 constexpr int OFF_B1 = OFF_W1 + TC_H * TC_MAX_D * 4;          // f32 [128]
 constexpr int OFF_B2 = OFF_B1 + TC_H * 4;
 constexpr int OFF_W3 = OFF_B2 + TC_H * 4;                     // f32 [4][128]
 constexpr int OFF_B3 = OFF_W3 + TC_MAX_OUT * TC_H * 4;        // f32 [4] (+pad)
 constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters][4][64]
-constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;  // f32 [64][4]
-constexpr int OFF_ROWF = OFF_MASK + TILE_M * TC_MAX_OUT * 4;  // f32 tgt, lpo, g, valid [64] each
-constexpr int OFF_ACT = OFF_ROWF + 4 * TILE_M * 4;            // int [64]
-constexpr int OFF_RED = OFF_ACT + TILE_M * 4;                 // double [16]
-constexpr int OFF_BAR = OFF_RED + 128;                         // 2 mbarriers + tmem base
+constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;      // f32 [2][64][4]
+constexpr int OFF_ROWF = OFF_MASK + 2 * TILE_M * TC_MAX_OUT * 4;       // f32 [2][3][64]: tgt, lpo, valid
+constexpr int OFF_ACT = OFF_ROWF + 2 * 3 * TILE_M * 4;                 // int [2][64]
+constexpr int OFF_HBITS = OFF_ACT + 2 * TILE_M * 4;                    // u32 [2][128 units][2]: h1 > 0 for 64 rows
+constexpr int OFF_RED = OFF_HBITS + 2 * TC_H * 2 * 4;                  // double [16]
+constexpr int OFF_BAR = OFF_RED + 128;                                 // 3 mbarriers + tmem base
 constexpr int TC_SMEM_BYTES = OFF_BAR + 32;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
+static_assert(TILE_M * TC_MAX_D == TC_THREADS, "one observation element per thread in the input fetch");
+static_assert(TC_H * (TC_H + 1) * 4 <= 6 * X_PLANE, "flush staging must fit in the operand planes");
 
 // 16 values per lane: lane l returns the total over the 32 lanes for c == (l & 15)
 __device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
@@ -80,9 +87,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     float *b1_s = reinterpret_cast<float *>(smem + OFF_B1), *b2_s = reinterpret_cast<float *>(smem + OFF_B2);
     float *w3_s = reinterpret_cast<float *>(smem + OFF_W3), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
     float *vpart_s = reinterpret_cast<float *>(smem + OFF_VPART), *mask_s = reinterpret_cast<float *>(smem + OFF_MASK);
-    float *tgt_s = reinterpret_cast<float *>(smem + OFF_ROWF), *lpo_s = tgt_s + TILE_M, *g_s = tgt_s + 2 * TILE_M,
-          *valid_s = tgt_s + 3 * TILE_M;
+    float *rowf_s = reinterpret_cast<float *>(smem + OFF_ROWF);
     int *act_s = reinterpret_cast<int *>(smem + OFF_ACT);
+    uint32_t *hbits_s = reinterpret_cast<uint32_t *>(smem + OFF_HBITS);
     double *red_s = reinterpret_cast<double *>(smem + OFF_RED);
     uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1, *bar3 = bar1 + 2;
     uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar3 + 1);
@@ -141,7 +148,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, false),
                        ID_G3 = idesc_bf16(128, 128, true, true);
 
-    // thread-local gradient accumulators for hidden unit j over this thread's half of the rows
+    // thread-local gradient accumulators for hidden unit j over this thread's quarter of the rows.
     // dW2 row j, this warp's 32 in-units: drained from TMEM after every tile.  The tensor core adds into
     // its fp32 accumulator with truncation (measured bias -4e-8 per MMA), so letting dW2 ride in TMEM
     // across tiles cost ~4e-6 of accuracy after 8 tiles; 24 MMAs per drain keep it at the CUDA-core level.
@@ -158,46 +165,63 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     int since_flush = 0;
     double *my_partials = a.partials + (size_t)blockIdx.x * a.n_params;
     const int64_t num_tiles = (a.n + TILE_M - 1) / TILE_M;
-    uint32_t parity = 0;
 
-    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, parity ^= 1u) {
+    // ---- per-tile building blocks ----------------------------------------------------------------------
+    // the inputs of a tile travel global -> registers (one tile ahead) -> shared memory buffer b
+    float pre_obs = 0.f, pre_mask = 1.f, pre_tgt = 0.f, pre_lpo = 0.f;
+    int pre_act = 0, pre_rows = 0;
+    auto fetch = [&](int64_t tile) {
         const int64_t row0 = tile * TILE_M;
         const int rows = (int)min((int64_t)TILE_M, a.n - row0);
-
-        // ---- P0: tile inputs ----------------------------------------------------------------------
-        for (int i = tid; i < TILE_M * TC_MAX_D; i += TC_THREADS) {
-            const int m = i / TC_MAX_D, c = i - m * TC_MAX_D;
-            obs_s[i] = (m < rows && c < d) ? __ldcs(a.obs + (row0 + m) * d + c) : 0.f;
+        pre_rows = rows;
+        {
+            const int m = tid / TC_MAX_D, c = tid - m * TC_MAX_D;
+            pre_obs = (m < rows && c < d) ? __ldcs(a.obs + (row0 + m) * d + c) : 0.f;
         }
-        if (MODE != MODE_VALUE)
-            for (int i = tid; i < TILE_M * TC_MAX_OUT; i += TC_THREADS) {
-                const int m = i / TC_MAX_OUT, c = i - m * TC_MAX_OUT;
-                mask_s[i] = (m < rows && c < out) ? __ldcs(a.mask + (row0 + m) * out + c) : 1.f;
-            }
-        if (tid < TILE_M) {
-            const bool ok = tid < rows;
-            valid_s[tid] = ok ? 1.f : 0.f;
+        if (MODE != MODE_VALUE && tid < TILE_M * TC_MAX_OUT) {
+            const int m = tid / TC_MAX_OUT, c = tid - m * TC_MAX_OUT;
+            pre_mask = (m < rows && c < out) ? __ldcs(a.mask + (row0 + m) * out + c) : 1.f;
+        }
+        if (tid >= TC_THREADS - TILE_M) {  // the last two warps fetch the per-row scalars
+            const int m = tid - (TC_THREADS - TILE_M);
+            const bool ok = m < rows;
             if (MODE == MODE_VALUE) {
-                tgt_s[tid] = ok ? a.ret[row0 + tid] : 0.f;
-                act_s[tid] = 0;
+                pre_tgt = ok ? __ldcs(a.ret + row0 + m) : 0.f;
             } else {
-                tgt_s[tid] = ok ? __fdiv_rn(a.adv[row0 + tid] - mean, sd) : 0.f;  // replay_buffer.py:105
-                lpo_s[tid] = ok ? a.logp_old[row0 + tid] : 0.f;
-                const int at = ok ? (int)a.act[row0 + tid] : 0;
-                act_s[tid] = min(max(at, 0), out - 1);
+                pre_tgt = ok ? __ldcs(a.adv + row0 + m) : 0.f;
+                pre_lpo = ok ? __ldcs(a.logp_old + row0 + m) : 0.f;
+                pre_act = ok ? (int)__ldcs(a.act + row0 + m) : 0;
             }
         }
-        __syncthreads();
-
-        // ---- P1: H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) ----
+    };
+    auto stash = [&](int b) {
+        obs_s[b * TILE_M * TC_MAX_D + tid] = pre_obs;
+        if (MODE != MODE_VALUE && tid < TILE_M * TC_MAX_OUT) mask_s[b * TILE_M * TC_MAX_OUT + tid] = pre_mask;
+        if (tid >= TC_THREADS - TILE_M) {
+            const int m = tid - (TC_THREADS - TILE_M);
+            const bool ok = m < pre_rows;
+            float *rf = rowf_s + b * 3 * TILE_M;
+            rf[2 * TILE_M + m] = ok ? 1.f : 0.f;
+            if (MODE == MODE_VALUE) {
+                rf[m] = pre_tgt;
+            } else {
+                rf[m] = ok ? __fdiv_rn(pre_tgt - mean, sd) : 0.f;  // replay_buffer.py:105
+                rf[TILE_M + m] = pre_lpo;
+                act_s[b * TILE_M + m] = min(max(pre_act, 0), out - 1);
+            }
+        }
+    };
+    // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) + the relu bit mask
+    auto stage1 = [&](int b) {
+        const float *ob = obs_s + b * TILE_M * TC_MAX_D;
 #pragma unroll 1
         for (int it = tid; it < TILE_M * (TC_H / 8); it += TC_THREADS) {
-            const int r = it & (TILE_M - 1), ch = it >> 6;
+            const int r = it & (TILE_M - 1), ch = it >> 6;  // a warp: 32 consecutive rows of one chunk
             float4 x[TC_MAX_D / 4];
 #pragma unroll
             for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                x[i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&obs_s[r * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
-            uint32_t w1[4], w2[4], w3[4];
+                x[i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&ob[r * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            uint32_t w1[4], w2[4], w3[4], bits = 0u;
 #pragma unroll
             for (int e = 0; e < 8; e += 2) {
                 Trunc3 s[2];
@@ -207,11 +231,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                     float acc = b1_s[u];
 #pragma unroll
                     for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                        if (4 * i4 < d) {  // W1 rows are zero padded to 16
+                        if (4 * i4 < d) {  // W1 rows are zero padded
                             const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
                             acc = fmaf(x[i4].x, w.x, acc), acc = fmaf(x[i4].y, w.y, acc);
                             acc = fmaf(x[i4].z, w.z, acc), acc = fmaf(x[i4].w, w.w, acc);
                         }
+                    const unsigned bal = __ballot_sync(0xffffffffu, acc > 0.f);  // 32 rows of unit u
+                    if (lane == e + t) bits = bal;
                     s[t] = trunc3(fmaxf(acc, 0.f));
                 }
                 w1[e >> 1] = pack_hi16(s[0].t1, s[1].t1), w2[e >> 1] = pack_hi16(s[0].t2, s[1].t2), w3[e >> 1] = pack_hi16(s[0].t3, s[1].t3);
@@ -220,23 +246,44 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
             *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
             *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(w3[0], w3[1], w3[2], w3[3]);
+            if (lane < 8) hbits_s[(b * TC_H + 8 * ch + lane) * 2 + ((r >> 5) & 1)] = bits;
         }
+    };
+    auto issue_g1 = [&]() {  // called by all 32 lanes of warp 0
+        fence_after_sync();
+        issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
+        mma_commit_warp(bar1);
+    };
+
+    // ---- pipeline prologue: inputs and H1 of the first tile, G1 in flight ---------------------------------
+    if ((int64_t)blockIdx.x < num_tiles) {
+        fetch(blockIdx.x);
+        stash(0);
+        __syncthreads();
+        stage1(0);
         fence_smem_to_async();
         fence_before_sync();
         __syncthreads();
+        if (warp == 0) issue_g1();
+    }
 
-        // ---- P2: G1 on the tensor core --------------------------------------------------------------
-        if (tid == 0) {
-            fence_after_sync();
-            issue_gemm_bf16x3(tmem + TM_D1, W2_k, H1_k, ID_G1, TC_H / 16, false);
-            mma_commit(bar1);
-        }
+    int k = 0;
+    for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
+        const int b = k & 1;
+        const uint32_t parity = (uint32_t)(k & 1);
+        const int64_t next = tile + gridDim.x;
+        const bool has_next = next < num_tiles;
+        ++since_flush;
+        const bool flush_now = since_flush == FLUSH_TILES || !has_next;
+        const float *rf = rowf_s + b * 3 * TILE_M;
+        if (has_next) fetch(next);  // global loads in flight under G1 and epilogue 1
+
         mbar_wait(bar1, parity);
         fence_after_sync();
 
-        // ---- P3: epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) ---------------------------
-        float h2[TC_RPT];
+        // ---- epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) -------------------------------------
         {
+            float h2[TC_RPT];
             tmem_ld16(tmem_lane + TM_D1 + TC_RPT * rq, h2);
             const float b2 = b2_s[j];
 #pragma unroll
@@ -249,67 +296,77 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 const float tot = reduce_scatter16(p, lane);  // row 16*rq + (lane & 15), summed over this warp's 32 units
                 if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
-        }
-        __syncthreads();
-        if (tid < TILE_M) {  // per-row loss and dhead
-            const int m = tid;
-            const bool ok = valid_s[m] != 0.f;
-            float head[TC_MAX_OUT];
-#pragma unroll
-            for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
-                head[o_] = ((vpart_s[(0 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(1 * TC_MAX_OUT + o_) * TILE_M + m]) +
-                            (vpart_s[(2 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(3 * TC_MAX_OUT + o_) * TILE_M + m])) +
-                           b3_s[o_];
-            if (MODE == MODE_VALUE) {
-                const float diff = head[0] - tgt_s[m];
-                if (ok) l0 += (double)diff * (double)diff;
-                const float g = ok ? a.inv_n * (2.f * diff) : 0.f;  // REINFORCE.py:160 backward
-                g_s[m] = g;
-                db3acc[0] += g;
-            } else {
-                float mx = -INFINITY;
+            __syncthreads();
+            // per-row loss and dhead: lane l of every warp works out row 16*rq + (l & 15); the four unit
+            // quarters do it redundantly (it is a handful of instructions), only q == 0 keeps the sums
+            float g_lane;
+            int at_lane = 0;
+            {
+                const int m = TC_RPT * rq + (lane & (TC_RPT - 1));
+                const bool ok = rf[2 * TILE_M + m] != 0.f;
+                const bool keeper = q == 0 && lane < TC_RPT;
+                float head[TC_MAX_OUT];
 #pragma unroll
                 for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
-                    if (o_ < out) {
-                        head[o_] = head[o_] + (mask_s[m * TC_MAX_OUT + o_] - 1.f) * 1e8f;  // kernel.py:23-26
-                        mx = fmaxf(mx, head[o_]);
+                    head[o_] = ((vpart_s[(0 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(1 * TC_MAX_OUT + o_) * TILE_M + m]) +
+                                (vpart_s[(2 * TC_MAX_OUT + o_) * TILE_M + m] + vpart_s[(3 * TC_MAX_OUT + o_) * TILE_M + m])) +
+                               b3_s[o_];
+                if (MODE == MODE_VALUE) {
+                    const float diff = head[0] - rf[m];
+                    if (ok && keeper) l0 += (double)diff * (double)diff;
+                    g_lane = ok ? a.inv_n * (2.f * diff) : 0.f;  // REINFORCE.py:160 backward
+                    if (keeper) db3acc[0] += g_lane;
+                } else {
+                    const float *mk = mask_s + b * TILE_M * TC_MAX_OUT;
+                    float mx = -INFINITY;
+#pragma unroll
+                    for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                        if (o_ < out) {
+                            head[o_] = head[o_] + (mk[m * TC_MAX_OUT + o_] - 1.f) * 1e8f;  // kernel.py:23-26
+                            mx = fmaxf(mx, head[o_]);
+                        }
+                    float se = 0.f;
+#pragma unroll
+                    for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                        if (o_ < out) se += expf(head[o_] - mx);
+                    at_lane = act_s[b * TILE_M + m];
+                    float ent = 0.f, lg_a = 0.f;
+#pragma unroll
+                    for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
+                        if (o_ < out) {
+                            ent += fmaxf(head[o_], -3.402823466e38f) * (expf(head[o_] - mx) / se);
+                            if (o_ == at_lane) lg_a = head[o_];
+                        }
+                    const float advn = rf[m];
+                    if (ok && keeper) {
+                        l0 += (double)(lg_a * advn);  // logp is the raw masked logit
+                        l1 += (double)(rf[TILE_M + m] - lg_a);
+                        l2 += (double)ent;
                     }
-                float se = 0.f;
+                    g_lane = ok ? (-a.inv_n) * advn : 0.f;
+                    if (keeper)
 #pragma unroll
-                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
-                    if (o_ < out) se += expf(head[o_] - mx);
-                const int at = act_s[m];
-                float ent = 0.f, lg_a = 0.f;
-#pragma unroll
-                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
-                    if (o_ < out) {
-                        ent += fmaxf(head[o_], -3.402823466e38f) * (expf(head[o_] - mx) / se);
-                        if (o_ == at) lg_a = head[o_];
-                    }
-                const float advn = tgt_s[m];
-                if (ok) {
-                    l0 += (double)(lg_a * advn);  // logp is the raw masked logit
-                    l1 += (double)(lpo_s[m] - lg_a);
-                    l2 += (double)ent;
+                        for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) db3acc[o_] += (o_ == at_lane) ? g_lane : 0.f;
                 }
-                const float g = ok ? (-a.inv_n) * advn : 0.f;
-                g_s[m] = g;
-#pragma unroll
-                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) db3acc[o_] += (o_ == at) ? g : 0.f;
             }
-        }
-        __syncthreads();
-        {  // dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2
+            // dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2
             float dbl = 0.f;
+            const float w3j = w3_s[j];
 #pragma unroll
             for (int c = 0; c < TC_RPT; ++c) {
                 const int m = TC_RPT * rq + c;
-                const float g = g_s[m];
-                const int at = act_s[m];
-                const float dz = h2[c] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
-                const float gh = g * h2[c];
+                const float g = __shfl_sync(0xffffffffu, g_lane, c);
+                float dz;
+                if (MODE == MODE_VALUE) {
+                    dz = h2[c] > 0.f ? g * w3j : 0.f;
+                    dW3acc[0] = fmaf(g, h2[c], dW3acc[0]);
+                } else {
+                    const int at = __shfl_sync(0xffffffffu, at_lane, c);
+                    dz = h2[c] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
+                    const float gh = g * h2[c];
 #pragma unroll
-                for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
+                    for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
+                }
                 dbl += dz;
                 const Trunc3 s = trunc3(dz);
                 const int o = x_off_bytes(m, j, TILE_M);
@@ -323,43 +380,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         fence_before_sync();
         __syncthreads();
 
-        // ---- P4: G3 (dW2 accumulates in TMEM) and G2 -------------------------------------------------------
-        if (tid == 0) {
+        // ---- G3 first (it frees the H1 planes), then G2 ---------------------------------------------------------
+        if (warp == 0) {
             fence_after_sync();
-            // G2 first: epilogue 2 only needs D2 and runs while the tensor core is still busy with G3
-            issue_gemm_bf16x3(tmem + TM_D2, W2_mn, DZ_k, ID_G2, TC_H / 16, false);
-            mma_commit(bar2);
-            issue_gemm_bf16x3(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, TILE_M / 16, false);
-            mma_commit(bar3);
+            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, false);
+            mma_commit_warp(bar3);
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_k, ID_G2, false);
+            mma_commit_warp(bar2);
         }
-        mbar_wait(bar2, parity);
-        fence_after_sync();
+        if (has_next) stash(b ^ 1);
 
-        // ---- P5: epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
-        {
-            float dh[TC_RPT];
-            tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
-            float dbl = 0.f;
-#pragma unroll
-            for (int c = 0; c < TC_RPT; ++c) {
-                const int m = TC_RPT * rq + c;
-                const unsigned short hb = *reinterpret_cast<const unsigned short *>(h1_p + x_off_bytes(m, j, TILE_M));
-                // h1 >= 0 after the ReLU; its leading bf16 part is zero iff h1 is (h1 < 2^-126 aside)
-                const float dz1 = (hb & 0x7fffu) != 0 ? dh[c] : 0.f;
-                dbl += dz1;
-#pragma unroll
-                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
-                    if (4 * i4 < d) {
-                        const float4 t = *reinterpret_cast<const float4 *>(&obs_s[m * TC_MAX_D + 4 * i4]);
-                        dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
-                        dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
-                        dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
-                        dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
-                    }
-                }
-            }
-            db1acc += dbl;
-        }
         // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's quarter of the in units) -------------
         mbar_wait(bar3, parity);
         fence_after_sync();
@@ -370,10 +400,48 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             for (int c = 0; c < 32; ++c) dW2sum[c] += v[c];
         }
 
+        // ---- stage 1 of the next tile under G2; its G1 under epilogue 2 ------------------------------------
+        const bool early_next = has_next && !flush_now;
+        if (early_next) {
+            fence_before_sync();
+            __syncthreads();  // the stashed inputs are visible; every warp saw G3 retire (H1 planes are free)
+            stage1(b ^ 1);
+            fence_smem_to_async();
+            fence_before_sync();
+            __syncthreads();
+            if (warp == 0) issue_g1();
+        }
+
+        // ---- epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
+        mbar_wait(bar2, parity);
+        fence_after_sync();
+        {
+            float dh[TC_RPT];
+            tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
+            const uint32_t hb = hbits_s[(b * TC_H + j) * 2 + (rq >> 1)] >> (TC_RPT * (rq & 1));
+            const float *ob = obs_s + b * TILE_M * TC_MAX_D;
+            float dbl = 0.f;
+#pragma unroll
+            for (int c = 0; c < TC_RPT; ++c) {
+                const int m = TC_RPT * rq + c;
+                const float dz1 = ((hb >> c) & 1u) ? dh[c] : 0.f;
+                dbl += dz1;
+#pragma unroll
+                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
+                    if (4 * i4 < d) {
+                        const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
+                        dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
+                        dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
+                        dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
+                        dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
+                    }
+                }
+            }
+            db1acc += dbl;
+        }
+
         // ---- spill the f32 window into the CTA's float64 partials -------------------------------------------
-        ++since_flush;
-        const bool last = tile + gridDim.x >= num_tiles;
-        if (since_flush == FLUSH_TILES || last) {
+        if (flush_now) {
             since_flush = 0;
             auto put = [&](int64_t p, float v) {
                 if (first_flush)
@@ -381,10 +449,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 else
                     my_partials[p] += (double)v;
             };
-            // dW2 (128 x 128 f32) is transposed through shared memory (the H1 and dz planes are idle:
-            // 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
+            // dW2 (128 x 128 f32) is transposed through shared memory (no GEMM is in flight: the H1 and dz
+            // planes are idle, 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
             float *w2stage = reinterpret_cast<float *>(h1_p);  // [128][129]
-            __syncthreads();  // every warp has finished epilogue 2, which still reads the H1 planes
+            __syncthreads();  // every warp has seen G2 and G3 retire
 #pragma unroll
             for (int c = 0; c < 32; ++c) {
                 w2stage[j * 129 + 32 * rq + c] = dW2sum[c];
@@ -403,8 +471,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 }
             }
             __syncthreads();
-            // per-unit accumulators: the row groups meet in shared memory (the dz planes are idle now)
-            float *stage = reinterpret_cast<float *>(dz_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
+            // per-unit accumulators: the row groups meet in shared memory
+            float *stage = reinterpret_cast<float *>(h1_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
             constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
             float *mine = stage + (rq * TC_H + j) * S;
             mine[0] = db1acc, mine[1] = db2acc;
@@ -413,15 +481,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
             for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
             float *stage3 = stage + TC_RG * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
-            if (tid < TILE_M)
+            if (q == 0 && lane < TC_RPT)
 #pragma unroll
-                for (int i = 0; i < TC_MAX_OUT; ++i) stage3[tid * TC_MAX_OUT + i] = db3acc[i];
+                for (int i = 0; i < TC_MAX_OUT; ++i) stage3[(TC_RPT * rq + lane) * TC_MAX_OUT + i] = db3acc[i];
             __syncthreads();
             if (tid < TC_H) {
-                auto tot = [&](int k) {
+                auto tot = [&](int kk) {
                     float t = 0.f;
 #pragma unroll
-                    for (int g_ = 0; g_ < TC_RG; ++g_) t += stage[(g_ * TC_H + tid) * S + k];
+                    for (int g_ = 0; g_ < TC_RG; ++g_) t += stage[(g_ * TC_H + tid) * S + kk];
                     return t;
                 };
                 put(nd.ob1() + tid, tot(0));
@@ -440,24 +508,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
             for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
             first_flush = false;
+            if (has_next) {  // restart the pipeline: the staging area becomes the H1 planes again
+                fence_before_sync();
+                __syncthreads();
+                stage1(b ^ 1);
+                fence_smem_to_async();
+                fence_before_sync();
+                __syncthreads();
+                if (warp == 0) issue_g1();
+            }
         }
-        fence_before_sync();
-        __syncthreads();  // obs / H1 / dz planes and TMEM D1, D2 are free for the next tile
     }
 
-    // ---- loss sums (rows live in threads 0..63) ------------------------------------------------------------
+    // ---- loss sums (rows live in lanes 0..15 of the q == 0 warps) --------------------------------------------
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) {
         l0 += __shfl_xor_sync(0xffffffffu, l0, dd);
         l1 += __shfl_xor_sync(0xffffffffu, l1, dd);
         l2 += __shfl_xor_sync(0xffffffffu, l2, dd);
     }
-    if (lane == 0 && warp < 2) red_s[warp * 4 + 0] = l0, red_s[warp * 4 + 1] = l1, red_s[warp * 4 + 2] = l2;
+    if (lane == 0 && q == 0) red_s[rq * 4 + 0] = l0, red_s[rq * 4 + 1] = l1, red_s[rq * 4 + 2] = l2;
     fence_before_sync();
     __syncthreads();
     if (tid == 0 && a.loss_partials) {
         double *lp = a.loss_partials + (size_t)blockIdx.x * 4;
-        lp[0] = red_s[0] + red_s[4], lp[1] = red_s[1] + red_s[5], lp[2] = red_s[2] + red_s[6], lp[3] = 0.0;
+        lp[0] = (red_s[0] + red_s[4]) + (red_s[8] + red_s[12]);
+        lp[1] = (red_s[1] + red_s[5]) + (red_s[9] + red_s[13]);
+        lp[2] = (red_s[2] + red_s[6]) + (red_s[10] + red_s[14]);
+        lp[3] = 0.0;
     }
     if (warp == 0) tmem_dealloc(tmem, TM_COLS);
 }

@@ -101,3 +101,86 @@ extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *
     tc_gemm_test_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(mode, A, B, D);
     return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;
 }
+
+// ---- micro-benchmark: how fast does one thread issue, and the tensor core retire, M=128 x N x 16 MMAs? -----
+namespace rrl {
+namespace {
+using namespace tc;
+__global__ void __launch_bounds__(128, 1) tc_rate_kernel(int N, int a_mn, int b_mn, int count, int uniform_issue, long long *out)
+{
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const uint32_t planeA = x_plane_bytes(128, 128), planeB = x_plane_bytes(N, 128);
+    for (uint32_t i = tid; i < (planeA + planeB) / 4; i += 128) reinterpret_cast<uint32_t *>(smem)[i] = 0;
+    if (warp == 0) tmem_alloc(&tmem_base_s, 256);
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    fence_smem_to_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = tmem_base_s;
+    if (uniform_issue && warp == 0) {
+        // the whole warp runs the loop; descriptors stay warp-uniform; one elected lane issues
+        const uint32_t abase = smem_u32(smem), bbase = smem_u32(smem + planeA);
+        const uint32_t a_lbo = a_mn ? 128 : x_chunk_bytes(128), a_sbo = a_mn ? x_chunk_bytes(128) : 128;
+        const uint32_t b_lbo = b_mn ? 128 : x_chunk_bytes(N), b_sbo = b_mn ? x_chunk_bytes(N) : 128;
+        const uint32_t a_k = a_mn ? 256 : 2 * x_chunk_bytes(128), b_k = b_mn ? 256 : 2 * x_chunk_bytes(N);
+        const uint32_t idesc = idesc_bf16(128, N, a_mn != 0, b_mn != 0);
+        const uint64_t da = smem_desc(abase, a_lbo, a_sbo), db = smem_desc(bbase, b_lbo, b_sbo);
+        const int ksteps = (a_mn || b_mn) ? min(8, N / 16) : 8;
+        const long long t0 = clock64();
+        for (int i = 0; i < count; i += 4) {
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int ss = s % ksteps;
+                mma_bf16_elect(tmem, da + ((ss * a_k) >> 4), db + ((ss * b_k) >> 4), idesc, (i + s) > 0);
+            }
+        }
+        if (elect_one()) mma_commit(&bar);
+        __syncwarp();
+        const long long t1 = clock64();
+        mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        if (tid == 0) out[0] = t1 - t0, out[1] = t2 - t0;
+    }
+    if (!uniform_issue && tid == 0) {
+        OperandDesc a, b;
+        a.base = smem_u32(smem), b.base = smem_u32(smem + planeA);
+        if (a_mn) a.sbo = x_chunk_bytes(128), a.lbo = 128, a.kstep = 256;
+        else a.lbo = x_chunk_bytes(128), a.sbo = 128, a.kstep = 2 * x_chunk_bytes(128);
+        if (b_mn) b.sbo = x_chunk_bytes(N), b.lbo = 128, b.kstep = 256;
+        else b.lbo = x_chunk_bytes(N), b.sbo = 128, b.kstep = 2 * x_chunk_bytes(N);
+        const uint32_t idesc = idesc_bf16(128, N, a_mn != 0, b_mn != 0);
+        const int ksteps = (a_mn || b_mn) ? min(8, N / 16) : 8;
+        const long long t0 = clock64();
+        for (int i = 0; i < count; ++i) {
+            const int s = i % ksteps;
+            mma_bf16(tmem, smem_desc(a.base + s * a.kstep, a.lbo, a.sbo), smem_desc(b.base + s * b.kstep, b.lbo, b.sbo), idesc, i > 0);
+        }
+        mma_commit(&bar);
+        const long long t1 = clock64();
+        mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        out[0] = t1 - t0, out[1] = t2 - t0;
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, 256);
+}
+}  // namespace
+}  // namespace rrl
+
+extern "C" int32_t rrl_debug_tc_rate(int32_t N, int32_t a_mn, int32_t b_mn, int32_t count, int32_t uniform_issue, long long *out_dev, void *stream)
+{
+    using namespace rrl;
+    if (N < 16 || N > 256 || N % 16 || count < 4 || count % 4 || !out_dev) return RRL_EINVAL;
+    const size_t smem = (size_t)rrl::tc::x_plane_bytes(128, 128) + rrl::tc::x_plane_bytes(N, 128);
+    if (cudaFuncSetAttribute(tc_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
+    tc_rate_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(N, a_mn, b_mn, count, uniform_issue, out_dev);
+    return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;
+}
