@@ -33,8 +33,12 @@ constexpr int TC_MAX_OUT = 4;
 constexpr int W_PLANE = tc::x_plane_bytes(TC_H, TC_H);    // bytes of one bf16 plane of W2
 constexpr int X_PLANE = tc::x_plane_bytes(TILE_M, TC_H);  // bytes of one bf16 plane of a 64-row activation tile
 constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H), X_CHUNK = tc::x_chunk_bytes(TILE_M);
-constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_COLS = 256;
-constexpr int TC_THREADS = 512;            // 16 warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
+constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_ACC = 256, TM_COLS = 512;
+constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
+// + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
+// entries deep).  17 warps are allocated as 20, i.e. 96 registers per thread: the dW2 sums therefore live in
+// TMEM (columns TM_ACC..), not in registers.
+constexpr int TC_CTA_THREADS = TC_THREADS + 32;
 constexpr int TC_RG = TC_THREADS / 128;    // row groups per tile
 constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (16)
 
@@ -50,12 +54,11 @@ constexpr int OFF_W3 = OFF_B2 + TC_H * 4;                     // f32 [4][128]
 constexpr int OFF_B3 = OFF_W3 + TC_MAX_OUT * TC_H * 4;        // f32 [4] (+pad)
 constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters][4][64]
 constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;      // f32 [2][64][4]
-constexpr int OFF_ROWF = OFF_MASK + 2 * TILE_M * TC_MAX_OUT * 4;       // f32 [2][3][64]: tgt, lpo, valid
-constexpr int OFF_ACT = OFF_ROWF + 2 * 3 * TILE_M * 4;                 // int [2][64]
-constexpr int OFF_HBITS = OFF_ACT + 2 * TILE_M * 4;                    // u32 [2][128 units][2]: h1 > 0 for 64 rows
+constexpr int OFF_ROWF = OFF_MASK + 2 * TILE_M * TC_MAX_OUT * 4;       // f32 [2][3][64]: ret | adv, logp_old, act
+constexpr int OFF_HBITS = OFF_ROWF + 2 * 3 * TILE_M * 4;                  // u32 [2][128 units][2]: h1 > 0 for 64 rows
 constexpr int OFF_RED = OFF_HBITS + 2 * TC_H * 2 * 4;                  // double [16]
-constexpr int OFF_BAR = OFF_RED + 128;                                 // 3 mbarriers + tmem base
-constexpr int TC_SMEM_BYTES = OFF_BAR + 32;
+constexpr int OFF_BAR = OFF_RED + 128;                                 // 5 mbarriers + tmem base
+constexpr int TC_SMEM_BYTES = OFF_BAR + 64;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
 static_assert(TILE_M * TC_MAX_D == TC_THREADS, "one observation element per thread in the input fetch");
 static_assert(TC_H * (TC_H + 1) * 4 <= 6 * X_PLANE, "flush staging must fit in the operand planes");
@@ -79,7 +82,7 @@ __device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
+__global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char *w2_p = smem + OFF_W2, *h1_p = smem + OFF_H1, *dz_p = smem + OFF_DZ;
@@ -88,11 +91,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     float *w3_s = reinterpret_cast<float *>(smem + OFF_W3), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
     float *vpart_s = reinterpret_cast<float *>(smem + OFF_VPART), *mask_s = reinterpret_cast<float *>(smem + OFF_MASK);
     float *rowf_s = reinterpret_cast<float *>(smem + OFF_ROWF);
-    int *act_s = reinterpret_cast<int *>(smem + OFF_ACT);
     uint32_t *hbits_s = reinterpret_cast<uint32_t *>(smem + OFF_HBITS);
     double *red_s = reinterpret_cast<double *>(smem + OFF_RED);
-    uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1, *bar3 = bar1 + 2;
-    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar3 + 1);
+    // bar1/2/3: G1/G2/G3 retired (tensor core -> workers); go1/go23: operands staged (workers -> MMA warp)
+    uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1, *bar3 = bar1 + 2, *go1 = bar1 + 3, *go23 = bar1 + 4;
+    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(bar1 + 5);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int q = warp & 3, rq = warp >> 2;  // TMEM lane quarter of this warp, which group of 16 rows
@@ -103,18 +106,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     // ---- one-time set-up: weights -> shared memory (W2 as three bf16 planes), TMEM, mbarriers ------
     {
         const float *W1 = a.params + nd.oW1(), *W2 = a.params + nd.oW2(), *W3 = a.params + nd.oW3();
-        for (int i = tid; i < TC_H * TC_H; i += TC_THREADS) {
+        for (int i = tid; i < TC_H * TC_H; i += TC_CTA_THREADS) {
             const Trunc3 s = trunc3(W2[i]);
             const int o = x_off_bytes(i >> 7, i & 127, TC_H);  // row = out unit, feature = in unit
             *reinterpret_cast<unsigned short *>(w2_p + o) = hi16(s.t1);
             *reinterpret_cast<unsigned short *>(w2_p + W_PLANE + o) = hi16(s.t2);
             *reinterpret_cast<unsigned short *>(w2_p + 2 * W_PLANE + o) = hi16(s.t3);
         }
-        for (int i = tid; i < TC_H * TC_MAX_D; i += TC_THREADS) {
+        for (int i = tid; i < TC_H * TC_MAX_D; i += TC_CTA_THREADS) {
             const int u = i / TC_MAX_D, c = i - u * TC_MAX_D;
             w1_s[i] = c < d ? W1[u * d + c] : 0.f;
         }
-        for (int i = tid; i < TC_MAX_OUT * TC_H; i += TC_THREADS) w3_s[i] = i < out * TC_H ? W3[i] : 0.f;
+        for (int i = tid; i < TC_MAX_OUT * TC_H; i += TC_CTA_THREADS) w3_s[i] = i < out * TC_H ? W3[i] : 0.f;
         if (tid < TC_H) b1_s[tid] = a.params[nd.ob1() + tid], b2_s[tid] = a.params[nd.ob2() + tid];
         if (tid < TC_MAX_OUT) b3_s[tid] = tid < out ? a.params[nd.ob3() + tid] : 0.f;
         if (warp == 0) tmem_alloc(tmem_s, TM_COLS);
@@ -122,6 +125,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             mbar_init(bar1, 1);
             mbar_init(bar2, 1);
             mbar_init(bar3, 1);
+            mbar_init(go1, 1);
+            mbar_init(go23, 1);
             mbar_fence_init();
         }
     }
@@ -152,9 +157,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     // dW2 row j, this warp's 32 in-units: drained from TMEM after every tile.  The tensor core adds into
     // its fp32 accumulator with truncation (measured bias -4e-8 per MMA), so letting dW2 ride in TMEM
     // across tiles cost ~4e-6 of accuracy after 8 tiles; 24 MMAs per drain keep it at the CUDA-core level.
-    float dW2sum[32];
-#pragma unroll
-    for (int i = 0; i < 32; ++i) dW2sum[i] = 0.f;
+    // (the sums themselves sit in TMEM columns TM_ACC.., same lane/column ownership as the drain)
     float dW3acc[TC_MAX_OUT], dW1acc[TC_MAX_D], db1acc = 0.f, db2acc = 0.f, db3acc[TC_MAX_OUT];
 #pragma unroll
     for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
@@ -167,50 +170,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     const int64_t num_tiles = (a.n + TILE_M - 1) / TILE_M;
 
     // ---- per-tile building blocks ----------------------------------------------------------------------
-    // the inputs of a tile travel global -> registers (one tile ahead) -> shared memory buffer b
-    float pre_obs = 0.f, pre_mask = 1.f, pre_tgt = 0.f, pre_lpo = 0.f;
-    int pre_act = 0, pre_rows = 0;
-    auto fetch = [&](int64_t tile) {
+    // the inputs of a tile travel global -> shared memory buffer b by cp.async (no registers), one tile ahead;
+    // out-of-range elements are zero filled (src-size 0)
+    auto cp4 = [&](void *dst, const float *src, bool ok) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(dst)), "l"(ok ? src : a.obs), "r"(ok ? 4 : 0) : "memory");
+    };
+    auto fetch_async = [&](int64_t tile, int b) {
         const int64_t row0 = tile * TILE_M;
         const int rows = (int)min((int64_t)TILE_M, a.n - row0);
-        pre_rows = rows;
         {
             const int m = tid / TC_MAX_D, c = tid - m * TC_MAX_D;
-            pre_obs = (m < rows && c < d) ? __ldcs(a.obs + (row0 + m) * d + c) : 0.f;
+            cp4(&obs_s[b * TILE_M * TC_MAX_D + tid], a.obs + (row0 + m) * d + c, m < rows && c < d);
         }
         if (MODE != MODE_VALUE && tid < TILE_M * TC_MAX_OUT) {
             const int m = tid / TC_MAX_OUT, c = tid - m * TC_MAX_OUT;
-            pre_mask = (m < rows && c < out) ? __ldcs(a.mask + (row0 + m) * out + c) : 1.f;
+            cp4(&mask_s[b * TILE_M * TC_MAX_OUT + tid], a.mask + (row0 + m) * out + c, m < rows && c < out);
         }
         if (tid >= TC_THREADS - TILE_M) {  // the last two warps fetch the per-row scalars
             const int m = tid - (TC_THREADS - TILE_M);
             const bool ok = m < rows;
-            if (MODE == MODE_VALUE) {
-                pre_tgt = ok ? __ldcs(a.ret + row0 + m) : 0.f;
-            } else {
-                pre_tgt = ok ? __ldcs(a.adv + row0 + m) : 0.f;
-                pre_lpo = ok ? __ldcs(a.logp_old + row0 + m) : 0.f;
-                pre_act = ok ? (int)__ldcs(a.act + row0 + m) : 0;
-            }
-        }
-    };
-    auto stash = [&](int b) {
-        obs_s[b * TILE_M * TC_MAX_D + tid] = pre_obs;
-        if (MODE != MODE_VALUE && tid < TILE_M * TC_MAX_OUT) mask_s[b * TILE_M * TC_MAX_OUT + tid] = pre_mask;
-        if (tid >= TC_THREADS - TILE_M) {
-            const int m = tid - (TC_THREADS - TILE_M);
-            const bool ok = m < pre_rows;
             float *rf = rowf_s + b * 3 * TILE_M;
-            rf[2 * TILE_M + m] = ok ? 1.f : 0.f;
             if (MODE == MODE_VALUE) {
-                rf[m] = pre_tgt;
+                cp4(&rf[m], a.ret + row0 + m, ok);
             } else {
-                rf[m] = ok ? __fdiv_rn(pre_tgt - mean, sd) : 0.f;  // replay_buffer.py:105
-                rf[TILE_M + m] = pre_lpo;
-                act_s[b * TILE_M + m] = min(max(pre_act, 0), out - 1);
+                cp4(&rf[m], a.adv + row0 + m, ok);
+                cp4(&rf[TILE_M + m], a.logp_old + row0 + m, ok);
+                cp4(&rf[2 * TILE_M + m], a.act + row0 + m, ok);
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    auto inputs_landed = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
     // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) + the relu bit mask
     auto stage1 = [&](int b) {
         const float *ob = obs_s + b * TILE_M * TC_MAX_D;
@@ -249,22 +239,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             if (lane < 8) hbits_s[(b * TC_H + 8 * ch + lane) * 2 + ((r >> 5) & 1)] = bits;
         }
     };
-    auto issue_g1 = [&]() {  // called by all 32 lanes of warp 0
-        fence_after_sync();
-        issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
-        mma_commit_warp(bar1);
-    };
+    // the 16 worker warps meet at a named barrier; the MMA warp never joins it
+    auto worker_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory"); };
+
+    if (warp == TC_THREADS / 32) {
+        {
+        // ---- the MMA warp: follows the workers' hand-offs tile by tile ------------------------------------
+        int k = 0;
+        if ((int64_t)blockIdx.x < num_tiles) {
+            mbar_wait(go1, 0);
+            fence_after_sync();
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
+            mma_commit_warp(bar1);
+        }
+        for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
+            mbar_wait(go23, (uint32_t)(k & 1));
+            fence_after_sync();
+            // G3 first: it frees the H1 planes for the next tile's stage 1, which then runs under G2
+            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, false);
+            mma_commit_warp(bar3);
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_k, ID_G2, false);
+            mma_commit_warp(bar2);
+            if (tile + gridDim.x < num_tiles) {
+                mbar_wait(go1, (uint32_t)((k + 1) & 1));
+                fence_after_sync();
+                issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
+                mma_commit_warp(bar1);
+            }
+        }
+        }
+    } else {
 
     // ---- pipeline prologue: inputs and H1 of the first tile, G1 in flight ---------------------------------
     if ((int64_t)blockIdx.x < num_tiles) {
-        fetch(blockIdx.x);
-        stash(0);
-        __syncthreads();
+        fetch_async(blockIdx.x, 0);
+        inputs_landed();
+        worker_sync();
         stage1(0);
         fence_smem_to_async();
         fence_before_sync();
-        __syncthreads();
-        if (warp == 0) issue_g1();
+        worker_sync();
+        if (tid == 0) mbar_arrive(go1);
     }
 
     int k = 0;
@@ -276,7 +291,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         ++since_flush;
         const bool flush_now = since_flush == FLUSH_TILES || !has_next;
         const float *rf = rowf_s + b * 3 * TILE_M;
-        if (has_next) fetch(next);  // global loads in flight under G1 and epilogue 1
+        const int rows_k = (int)min((int64_t)TILE_M, a.n - tile * TILE_M);
 
         mbar_wait(bar1, parity);
         fence_after_sync();
@@ -296,14 +311,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 const float tot = reduce_scatter16(p, lane);  // row 16*rq + (lane & 15), summed over this warp's 32 units
                 if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
-            __syncthreads();
+            worker_sync();  // (also: every warp has left the previous tile, whose input buffers are free again)
+            if (has_next) fetch_async(next, b ^ 1);
             // per-row loss and dhead: lane l of every warp works out row 16*rq + (l & 15); the four unit
             // quarters do it redundantly (it is a handful of instructions), only q == 0 keeps the sums
             float g_lane;
             int at_lane = 0;
             {
                 const int m = TC_RPT * rq + (lane & (TC_RPT - 1));
-                const bool ok = rf[2 * TILE_M + m] != 0.f;
+                const bool ok = m < rows_k;
                 const bool keeper = q == 0 && lane < TC_RPT;
                 float head[TC_MAX_OUT];
 #pragma unroll
@@ -313,23 +329,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                                b3_s[o_];
                 if (MODE == MODE_VALUE) {
                     const float diff = head[0] - rf[m];
-                    if (ok && keeper) l0 += (double)diff * (double)diff;
                     g_lane = ok ? a.inv_n * (2.f * diff) : 0.f;  // REINFORCE.py:160 backward
-                    if (keeper) db3acc[0] += g_lane;
+                    if (q == 0) {  // warp-uniform branch: the float64 pipe is slow, keep it to four warps
+                        if (ok && keeper) l0 += (double)diff * (double)diff;
+                        if (keeper) db3acc[0] += g_lane;
+                    }
                 } else {
                     const float *mk = mask_s + b * TILE_M * TC_MAX_OUT;
                     float mx = -INFINITY;
 #pragma unroll
                     for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
                         if (o_ < out) {
-                            head[o_] = head[o_] + (mk[m * TC_MAX_OUT + o_] - 1.f) * 1e8f;  // kernel.py:23-26
+                            head[o_] = head[o_] + ((ok ? mk[m * TC_MAX_OUT + o_] : 1.f) - 1.f) * 1e8f;  // kernel.py:23-26
                             mx = fmaxf(mx, head[o_]);
                         }
                     float se = 0.f;
 #pragma unroll
                     for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
                         if (o_ < out) se += expf(head[o_] - mx);
-                    at_lane = act_s[b * TILE_M + m];
+                    at_lane = ok ? min(max((int)rf[2 * TILE_M + m], 0), out - 1) : 0;
                     float ent = 0.f, lg_a = 0.f;
 #pragma unroll
                     for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
@@ -337,8 +355,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                             ent += fmaxf(head[o_], -3.402823466e38f) * (expf(head[o_] - mx) / se);
                             if (o_ == at_lane) lg_a = head[o_];
                         }
-                    const float advn = rf[m];
-                    if (ok && keeper) {
+                    const float advn = ok ? __fdiv_rn(rf[m] - mean, sd) : 0.f;  // replay_buffer.py:105
+                    if (q == 0 && ok && keeper) {
                         l0 += (double)(lg_a * advn);  // logp is the raw masked logit
                         l1 += (double)(rf[TILE_M + m] - lg_a);
                         l2 += (double)ent;
@@ -378,38 +396,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         }
         fence_smem_to_async();
         fence_before_sync();
-        __syncthreads();
+        worker_sync();
 
-        // ---- G3 first (it frees the H1 planes), then G2 ---------------------------------------------------------
-        if (warp == 0) {
-            fence_after_sync();
-            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, false);
-            mma_commit_warp(bar3);
-            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_k, ID_G2, false);
-            mma_commit_warp(bar2);
-        }
-        if (has_next) stash(b ^ 1);
+        if (tid == 0) mbar_arrive(go23);  // the MMA warp issues G3, then G2
 
         // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's quarter of the in units) -------------
         mbar_wait(bar3, parity);
         fence_after_sync();
-        {
-            float v[32];
-            tmem_ld32(tmem_lane + TM_DW2 + 32 * rq, v);
 #pragma unroll
-            for (int c = 0; c < 32; ++c) dW2sum[c] += v[c];
+        for (int hf = 0; hf < 2; ++hf) {
+            float v[16], s[16];
+            tmem_ld16(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v);
+            if (since_flush > 1) {
+                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, s);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) v[c] += s[c];
+            }
+            tmem_st16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
         }
 
         // ---- stage 1 of the next tile under G2; its G1 under epilogue 2 ------------------------------------
         const bool early_next = has_next && !flush_now;
+        if (has_next) inputs_landed();
         if (early_next) {
             fence_before_sync();
-            __syncthreads();  // the stashed inputs are visible; every warp saw G3 retire (H1 planes are free)
+            worker_sync();  // the next inputs are visible; every warp saw G3 retire (H1 planes are free)
             stage1(b ^ 1);
             fence_smem_to_async();
             fence_before_sync();
-            __syncthreads();
-            if (warp == 0) issue_g1();
+            worker_sync();
+            if (tid == 0) mbar_arrive(go1);
         }
 
         // ---- epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
@@ -452,13 +468,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             // dW2 (128 x 128 f32) is transposed through shared memory (no GEMM is in flight: the H1 and dz
             // planes are idle, 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
             float *w2stage = reinterpret_cast<float *>(h1_p);  // [128][129]
-            __syncthreads();  // every warp has seen G2 and G3 retire
+            worker_sync();  // every warp has seen G2 and G3 retire
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-                w2stage[j * 129 + 32 * rq + c] = dW2sum[c];
-                dW2sum[c] = 0.f;
+            for (int hf = 0; hf < 2; ++hf) {
+                float v[16];
+                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) w2stage[j * 129 + 32 * rq + 16 * hf + c] = v[c];
             }
-            __syncthreads();
+            worker_sync();
             {
                 double *dst = my_partials + nd.oW2();
                 double old[TC_H * TC_H / TC_THREADS];
@@ -470,7 +488,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                     __stcg(dst + idx, old[e] + (double)w2stage[(idx >> 7) * 129 + (idx & 127)]);
                 }
             }
-            __syncthreads();
+            worker_sync();
             // per-unit accumulators: the row groups meet in shared memory
             float *stage = reinterpret_cast<float *>(h1_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
             constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
@@ -484,7 +502,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             if (q == 0 && lane < TC_RPT)
 #pragma unroll
                 for (int i = 0; i < TC_MAX_OUT; ++i) stage3[(TC_RPT * rq + lane) * TC_MAX_OUT + i] = db3acc[i];
-            __syncthreads();
+            worker_sync();
             if (tid < TC_H) {
                 auto tot = [&](int kk) {
                     float t = 0.f;
@@ -510,15 +528,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             first_flush = false;
             if (has_next) {  // restart the pipeline: the staging area becomes the H1 planes again
                 fence_before_sync();
-                __syncthreads();
+                worker_sync();
                 stage1(b ^ 1);
                 fence_smem_to_async();
                 fence_before_sync();
-                __syncthreads();
-                if (warp == 0) issue_g1();
+                worker_sync();
+                if (tid == 0) mbar_arrive(go1);
             }
         }
     }
+    }  // worker warps
 
     // ---- loss sums (rows live in lanes 0..15 of the q == 0 warps) --------------------------------------------
 #pragma unroll
@@ -527,7 +546,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         l1 += __shfl_xor_sync(0xffffffffu, l1, dd);
         l2 += __shfl_xor_sync(0xffffffffu, l2, dd);
     }
-    if (lane == 0 && q == 0) red_s[rq * 4 + 0] = l0, red_s[rq * 4 + 1] = l1, red_s[rq * 4 + 2] = l2;
+    if (lane == 0 && q == 0 && warp < TC_THREADS / 32) red_s[rq * 4 + 0] = l0, red_s[rq * 4 + 1] = l1, red_s[rq * 4 + 2] = l2;
     fence_before_sync();
     __syncthreads();
     if (tid == 0 && a.loss_partials) {
@@ -554,10 +573,10 @@ int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, 
     (void)nd;
     if (mode == MODE_VALUE) {
         RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_VALUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_VALUE><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(a);
+        mlp_tc_kernel<MODE_VALUE><<<grid, TC_CTA_THREADS, TC_SMEM_BYTES, stream>>>(a);
     } else {
         RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_POLICY_REF>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_POLICY_REF><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(a);
+        mlp_tc_kernel<MODE_POLICY_REF><<<grid, TC_CTA_THREADS, TC_SMEM_BYTES, stream>>>(a);
     }
     RRL_CUDA_OK(cudaGetLastError(), err);
     return RRL_OK;
