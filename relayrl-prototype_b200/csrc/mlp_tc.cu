@@ -8,9 +8,10 @@
 //   stage 1:  H1 = relu(obs W1^T + b1)               CUDA cores (K = obs_dim is tiny) -> planes + relu bit mask
 //   G1:       D1^T[out x row] = W2 * H1^T            A = W2 (K-major),  B = H1 (K-major),  N = 64
 //   epilogue 1 (thread = hidden unit, 16 rows): h2 = relu(D1 + b2); head = W3 h2 (warp reduce-scatter);
-//       loss, dhead per row; dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2 accumulate thread-locally
-//   G3:       dW2[out x in] = dZ2^T * H1             A = dZ2 (MN-major), B = H1 (MN-major), N = 128, K = 64 rows
-//   G2:       D2^T[in x row] = W2^T * dZ2^T          A = W2 (MN-major), B = dZ2 (K-major),  N = 64
+//       loss, dhead per row; dz2 = dhead W3 [h2 > 0] -> planes stored transposed ([unit][row]: the owner of a
+//       unit writes 8 rows per 16-byte store); dW3, db2 accumulate thread-locally
+//   G3:       dW2[out x in] = dZ2^T * H1             A = dZ2^T (K-major), B = H1 (MN-major),   N = 128, K = 64 rows
+//   G2:       D2^T[in x row] = W2^T * dZ2^T          A = W2 (MN-major),   B = dZ2^T (MN-major), N = 64
 //   epilogue 2 (thread = hidden unit): dz1 = D2 [h1 > 0]; dW1, db1 accumulate thread-locally
 // Schedule (the operand planes are single buffered -- W2 + H1 + dZ2 fill shared memory -- so the overlap
 // comes from the order of work): G3 goes first; as soon as it retires the H1 planes are free and stage 1 of
@@ -33,6 +34,8 @@ constexpr int TC_MAX_OUT = 4;
 constexpr int W_PLANE = tc::x_plane_bytes(TC_H, TC_H);    // bytes of one bf16 plane of W2
 constexpr int X_PLANE = tc::x_plane_bytes(TILE_M, TC_H);  // bytes of one bf16 plane of a 64-row activation tile
 constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H), X_CHUNK = tc::x_chunk_bytes(TILE_M);
+// dZ2 is kept transposed: X layout of [unit][row], so that the thread that owns a unit stores 8 rows per 16 bytes
+constexpr int DZ_PLANE = tc::x_plane_bytes(TC_H, TILE_M), DZ_CHUNK = tc::x_chunk_bytes(TC_H);
 constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_ACC = 256, TM_COLS = 512;
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
@@ -46,7 +49,7 @@ constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (
 constexpr int OFF_W2 = 0;
 constexpr int OFF_H1 = OFF_W2 + 3 * W_PLANE;
 constexpr int OFF_DZ = OFF_H1 + 3 * X_PLANE;
-constexpr int OFF_OBS = OFF_DZ + 3 * X_PLANE;                 // f32 [2][64][8]
+constexpr int OFF_OBS = OFF_DZ + 3 * DZ_PLANE;                // f32 [2][64][8]
 constexpr int OFF_W1 = OFF_OBS + 2 * TILE_M * TC_MAX_D * 4;   // f32 [128][8]
 constexpr int OFF_B1 = OFF_W1 + TC_H * TC_MAX_D * 4;          // f32 [128]
 constexpr int OFF_B2 = OFF_B1 + TC_H * 4;
@@ -61,7 +64,7 @@ constexpr int OFF_BAR = OFF_RED + 128;                                 // 5 mbar
 constexpr int TC_SMEM_BYTES = OFF_BAR + 64;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
 static_assert(TILE_M * TC_MAX_D == TC_THREADS, "one observation element per thread in the input fetch");
-static_assert(TC_H * (TC_H + 1) * 4 <= 6 * X_PLANE, "flush staging must fit in the operand planes");
+static_assert(TC_H * (TC_H + 1) * 4 <= 3 * X_PLANE + 3 * DZ_PLANE, "flush staging must fit in the operand planes");
 
 // 16 values per lane: lane l returns the total over the 32 lanes for c == (l & 15)
 __device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
@@ -80,6 +83,20 @@ __device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
     }
     return p[0];
 }
+
+#ifdef RRL_TC_TIMING
+__device__ unsigned long long g_tc_timing[16];
+#define TCT_DECL long long tct_prev = clock64()
+#define TCT(slot)                                                                      \
+    do {                                                                               \
+        const long long tct_now = clock64();                                           \
+        if (blockIdx.x == 0 && lane == 0) atomicAdd(&g_tc_timing[slot], (unsigned long long)(tct_now - tct_prev)); \
+        tct_prev = tct_now;                                                            \
+    } while (0)
+#else
+#define TCT_DECL
+#define TCT(slot)
+#endif
 
 template <int MODE>
 __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
@@ -148,10 +165,12 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     H1_k.base = H1_mn.base = smem_u32(h1_p), H1_k.plane_bytes = H1_mn.plane_bytes = X_PLANE;
     H1_k.lbo = X_CHUNK, H1_k.sbo = 128, H1_k.kstep = 2 * X_CHUNK;
     H1_mn.sbo = X_CHUNK, H1_mn.lbo = 128, H1_mn.kstep = 256;
-    DZ_k = H1_k, DZ_mn = H1_mn;
-    DZ_k.base = DZ_mn.base = smem_u32(dz_p);
-    constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, false),
-                       ID_G3 = idesc_bf16(128, 128, true, true);
+    // dZ2^T [unit][row]: K-major as G3's A (M = unit, K = row), MN-major as G2's B (N = row, K = unit)
+    DZ_k.base = DZ_mn.base = smem_u32(dz_p), DZ_k.plane_bytes = DZ_mn.plane_bytes = DZ_PLANE;
+    DZ_k.lbo = DZ_CHUNK, DZ_k.sbo = 128, DZ_k.kstep = 2 * DZ_CHUNK;
+    DZ_mn.sbo = DZ_CHUNK, DZ_mn.lbo = 128, DZ_mn.kstep = 256;
+    constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, true),
+                       ID_G3 = idesc_bf16(128, 128, false, true);
 
     // thread-local gradient accumulators for hidden unit j over this thread's quarter of the rows.
     // dW2 row j, this warp's 32 in-units: drained from TMEM after every tile.  The tensor core adds into
@@ -252,19 +271,25 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
             mma_commit_warp(bar1);
         }
+        TCT_DECL;
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
             mbar_wait(go23, (uint32_t)(k & 1));
+            TCT(0);
             fence_after_sync();
             // G3 first: it frees the H1 planes for the next tile's stage 1, which then runs under G2
-            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_mn, H1_mn, ID_G3, false);
+            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_k, H1_mn, ID_G3, false);
             mma_commit_warp(bar3);
-            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_k, ID_G2, false);
+            TCT(1);
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_mn, ID_G2, false);
             mma_commit_warp(bar2);
+            TCT(2);
             if (tile + gridDim.x < num_tiles) {
                 mbar_wait(go1, (uint32_t)((k + 1) & 1));
+                TCT(3);
                 fence_after_sync();
                 issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
                 mma_commit_warp(bar1);
+                TCT(4);
             }
         }
         }
@@ -283,6 +308,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     }
 
     int k = 0;
+    TCT_DECL;
     for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
         const int b = k & 1;
         const uint32_t parity = (uint32_t)(k & 1);
@@ -294,6 +320,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         const int rows_k = (int)min((int64_t)TILE_M, a.n - tile * TILE_M);
 
         mbar_wait(bar1, parity);
+        TCT(5);
         fence_after_sync();
 
         // ---- epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) -------------------------------------
@@ -367,30 +394,37 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                         for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) db3acc[o_] += (o_ == at_lane) ? g_lane : 0.f;
                 }
             }
-            // dz2 = dhead W3 [h2 > 0] -> planes; dW3, db2
+            // dz2 = dhead W3 [h2 > 0] -> transposed planes (two 16-byte pieces of 8 rows per plane); dW3, db2
             float dbl = 0.f;
             const float w3j = w3_s[j];
+            uint32_t pk[3][TC_RPT / 2];
 #pragma unroll
-            for (int c = 0; c < TC_RPT; ++c) {
-                const int m = TC_RPT * rq + c;
-                const float g = __shfl_sync(0xffffffffu, g_lane, c);
-                float dz;
-                if (MODE == MODE_VALUE) {
-                    dz = h2[c] > 0.f ? g * w3j : 0.f;
-                    dW3acc[0] = fmaf(g, h2[c], dW3acc[0]);
-                } else {
-                    const int at = __shfl_sync(0xffffffffu, at_lane, c);
-                    dz = h2[c] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
-                    const float gh = g * h2[c];
+            for (int c = 0; c < TC_RPT; c += 2) {
+                Trunc3 s2[2];
 #pragma unroll
-                    for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
+                for (int t = 0; t < 2; ++t) {
+                    const float g = __shfl_sync(0xffffffffu, g_lane, c + t);
+                    float dz;
+                    if (MODE == MODE_VALUE) {
+                        dz = h2[c + t] > 0.f ? g * w3j : 0.f;
+                        dW3acc[0] = fmaf(g, h2[c + t], dW3acc[0]);
+                    } else {
+                        const int at = __shfl_sync(0xffffffffu, at_lane, c + t);
+                        dz = h2[c + t] > 0.f ? g * w3_s[at * TC_H + j] : 0.f;
+                        const float gh = g * h2[c + t];
+#pragma unroll
+                        for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) dW3acc[o_] += (o_ == at) ? gh : 0.f;
+                    }
+                    dbl += dz;
+                    s2[t] = trunc3(dz);
                 }
-                dbl += dz;
-                const Trunc3 s = trunc3(dz);
-                const int o = x_off_bytes(m, j, TILE_M);
-                *reinterpret_cast<unsigned short *>(dz_p + o) = hi16(s.t1);
-                *reinterpret_cast<unsigned short *>(dz_p + X_PLANE + o) = hi16(s.t2);
-                *reinterpret_cast<unsigned short *>(dz_p + 2 * X_PLANE + o) = hi16(s.t3);
+                pk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), pk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2), pk[2][c >> 1] = pack_hi16(s2[0].t3, s2[1].t3);
+            }
+#pragma unroll
+            for (int pl = 0; pl < 3; ++pl) {
+                unsigned char *dst = dz_p + pl * DZ_PLANE + (2 * rq) * DZ_CHUNK + j * 16;  // rows 16 rq .. +7, then +8 .. +15
+                *reinterpret_cast<uint4 *>(dst) = make_uint4(pk[pl][0], pk[pl][1], pk[pl][2], pk[pl][3]);
+                *reinterpret_cast<uint4 *>(dst + DZ_CHUNK) = make_uint4(pk[pl][4], pk[pl][5], pk[pl][6], pk[pl][7]);
             }
             db2acc += dbl;
         }
@@ -399,9 +433,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         worker_sync();
 
         if (tid == 0) mbar_arrive(go23);  // the MMA warp issues G3, then G2
+        TCT(6);
 
         // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's quarter of the in units) -------------
         mbar_wait(bar3, parity);
+        TCT(7);
         fence_after_sync();
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
@@ -427,9 +463,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             worker_sync();
             if (tid == 0) mbar_arrive(go1);
         }
+        TCT(8);
 
         // ---- epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
         mbar_wait(bar2, parity);
+        TCT(9);
         fence_after_sync();
         {
             float dh[TC_RPT];
@@ -456,6 +494,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             db1acc += dbl;
         }
 
+        TCT(10);
         // ---- spill the f32 window into the CTA's float64 partials -------------------------------------------
         if (flush_now) {
             since_flush = 0;
@@ -463,7 +502,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 if (first_flush)
                     my_partials[p] = (double)v;
                 else
-                    my_partials[p] += (double)v;
+                    atomicAdd(my_partials + p, (double)v);
             };
             // dW2 (128 x 128 f32) is transposed through shared memory (no GEMM is in flight: the H1 and dz
             // planes are idle, 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
@@ -478,14 +517,17 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             }
             worker_sync();
             {
+                // each float64 partial is owned by one thread: the first window stores, later windows add with
+                // fire-and-forget reductions (no load latency on the path; one thread per address => fixed order)
                 double *dst = my_partials + nd.oW2();
-                double old[TC_H * TC_H / TC_THREADS];
-#pragma unroll
-                for (int e = 0; e < TC_H * TC_H / TC_THREADS; ++e) old[e] = first_flush ? 0.0 : __ldcg(dst + tid + e * TC_THREADS);
-#pragma unroll
+#pragma unroll 8
                 for (int e = 0; e < TC_H * TC_H / TC_THREADS; ++e) {
                     const int idx = tid + e * TC_THREADS;
-                    __stcg(dst + idx, old[e] + (double)w2stage[(idx >> 7) * 129 + (idx & 127)]);
+                    const double w = (double)w2stage[(idx >> 7) * 129 + (idx & 127)];
+                    if (first_flush)
+                        __stcg(dst + idx, w);
+                    else
+                        atomicAdd(dst + idx, w);
                 }
             }
             worker_sync();
@@ -536,6 +578,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 if (tid == 0) mbar_arrive(go1);
             }
         }
+        TCT(11);
     }
     }  // worker warps
 
@@ -560,6 +603,18 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 }
 
 }  // namespace
+
+#ifdef RRL_TC_TIMING
+extern "C" int32_t rrl_debug_tc_timing(unsigned long long *out16, int32_t reset)
+{
+    if (out16 && cudaMemcpyFromSymbol(out16, g_tc_timing, sizeof(g_tc_timing)) != cudaSuccess) return RRL_ECUDA;
+    if (reset) {
+        unsigned long long z[16] = {};
+        if (cudaMemcpyToSymbol(g_tc_timing, z, sizeof(z)) != cudaSuccess) return RRL_ECUDA;
+    }
+    return RRL_OK;
+}
+#endif
 
 bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad)
 {

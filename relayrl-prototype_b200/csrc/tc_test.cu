@@ -12,6 +12,8 @@ using namespace tc;
 // mode 0: D[128 x 64]  = A[128 x 128] * B[64 x 128]^T      (A K-major, B K-major)     -- forward GEMM
 // mode 1: D[128 x 64]  = A[128 x 128]^T * B[64 x 128]^T    (A MN-major, B K-major)    -- data-gradient GEMM
 // mode 2: D[128 x 128] = A[64 x 128]^T * B[64 x 128]       (A MN-major, B MN-major)   -- weight-gradient GEMM
+// mode 3: D[128 x 128] = A[128 x 0:64] * B[64 x 128]       (A K-major,  B MN-major)   -- weight-gradient GEMM with
+//                                                                                         the transposed dZ2 planes
 // All inputs row-major fp32 [rows][128] in global memory.
 __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const float *__restrict__ A,
                                                               const float *__restrict__ B, float *__restrict__ D)
@@ -51,7 +53,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
     fence_after_sync();
     const uint32_t tmem = tmem_base_s;
 
-    const int N = mode == 2 ? 128 : 64;
+    const int N = mode >= 2 ? 128 : 64;
     if (tid == 0) {
         OperandDesc a, b;
         a.base = smem_u32(sa), a.plane_bytes = planeA;
@@ -66,10 +68,14 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
             a.sbo = x_chunk_bytes(RA), a.lbo = 128, a.kstep = 2 * 128;
             b.lbo = x_chunk_bytes(RB), b.sbo = 128, b.kstep = 2 * x_chunk_bytes(RB);
             ksteps = 8, idesc = idesc_bf16(128, 64, true, false);
-        } else {  // both: M/N = features, K = rows(64)
+        } else if (mode == 2) {  // both: M/N = features, K = rows(64)
             a.sbo = x_chunk_bytes(RA), a.lbo = 128, a.kstep = 2 * 128;
             b.sbo = x_chunk_bytes(RB), b.lbo = 128, b.kstep = 2 * 128;
             ksteps = 4, idesc = idesc_bf16(128, 128, true, true);
+        } else {  // A: M = rows(128), K = features 0..63; B: N = features, K = rows(64)
+            a.lbo = x_chunk_bytes(RA), a.sbo = 128, a.kstep = 2 * x_chunk_bytes(RA);
+            b.sbo = x_chunk_bytes(RB), b.lbo = 128, b.kstep = 2 * 128;
+            ksteps = 4, idesc = idesc_bf16(128, 128, false, true);
         }
         issue_gemm_bf16x3(tmem, a, b, idesc, ksteps, false);
         mma_commit(&bar);
@@ -95,7 +101,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
 extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *B, float *D, void *stream)
 {
     using namespace rrl;
-    if (mode < 0 || mode > 2 || !A || !B || !D) return RRL_EINVAL;
+    if (mode < 0 || mode > 3 || !A || !B || !D) return RRL_EINVAL;
     const size_t smem = 3 * (size_t)rrl::tc::x_plane_bytes(mode == 2 ? 64 : 128, 128) + 3 * (size_t)rrl::tc::x_plane_bytes(64, 128);
     if (cudaFuncSetAttribute(tc_gemm_test_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
     tc_gemm_test_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(mode, A, B, D);
