@@ -116,6 +116,10 @@ void rrl_config_defaults(rrl_config_t *cfg);
 /* REINFORCE.__init__ (REINFORCE.py:17-62).  Weights start at zero: call rrl_set_params. */
 int32_t rrl_learner_create(const rrl_config_t *cfg, rrl_learner_t **out);
 int32_t rrl_learner_destroy(rrl_learner_t *h);
+/* The CUDA stream (cudaStream_t) every call on this handle is ordered on.  No counterpart in the reference
+ * (its learner is synchronous CPU code); callers use it to order their own device work against the
+ * learner's, or to time calls with CUDA events (bench.py does). */
+int32_t rrl_learner_stream(const rrl_learner_t *h, void **stream);
 
 /* Flat parameters in torch.nn.Linear order W1,b1,W2,b2,W3,b3, W row-major [out,in]
  * (kernel.py:15-21; BaseKernel.py:25-39).  which: 0 = policy.pi_network, 1 = baseline.v_network. */

@@ -420,6 +420,13 @@ int32_t rrl_learner_create(const rrl_config_t *cfg, rrl_learner_t **out)
     return RRL_OK;
 }
 
+int32_t rrl_learner_stream(const rrl_learner_t *h, void **stream)
+{
+    if (!h || !stream) return RRL_EINVAL;
+    *stream = static_cast<void *>(h->stream);
+    return RRL_OK;
+}
+
 int32_t rrl_param_count(const rrl_learner_t *h, int32_t which, int64_t *n)
 {
     if (!h || !n || which < 0 || which > 1 || (which == 1 && !h->cfg.with_baseline)) return RRL_EINVAL;

@@ -54,6 +54,7 @@ SIGNATURES = {
     "rrl_config_defaults": (None, [C.POINTER(Config)]),
     "rrl_learner_create": (C.c_int32, [C.POINTER(Config), C.POINTER(_P)]),
     "rrl_learner_destroy": (C.c_int32, [_P]),
+    "rrl_learner_stream": (C.c_int32, [_P, C.POINTER(_P)]),
     "rrl_param_count": (C.c_int32, [_P, C.c_int32, C.POINTER(C.c_int64)]),
     "rrl_set_params": (C.c_int32, [_P, C.c_int32, _P, C.c_int64]),
     "rrl_get_params": (C.c_int32, [_P, C.c_int32, _P, C.c_int64]),

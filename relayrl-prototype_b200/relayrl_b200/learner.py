@@ -66,6 +66,13 @@ class Learner:
     def _ck(self, status):
         check(status, self._h)
 
+    @property
+    def stream(self):
+        """cudaStream_t (as an int) that every call on this learner is ordered on."""
+        st = C.c_void_p()
+        self._ck(self._L.rrl_learner_stream(self._h, C.byref(st)))
+        return st.value or 0
+
     # -- parameters (torch.nn.Linear order W1,b1,W2,b2,W3,b3; kernel.py:15-21) -----------------
     def param_count(self, which):
         n = C.c_int64()
