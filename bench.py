@@ -167,7 +167,7 @@ def run_reference(args):
         "impl": "reference", "metric": "learner transitions/sec", "value": value, "unit": "transitions/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, sample),
+        "config": workload_config(args, args.n),   # the GPU arm's workload; each step times a bounded sample of it
         "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": threads, "kind": "port",
                          "sample": sample_desc},
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

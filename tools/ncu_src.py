@@ -1,6 +1,10 @@
 import csv, sys
 rows=list(csv.reader(open(sys.argv[1])))
-hdr=rows[1]; data=rows[2:]
+# a report with several kernels has one block per kernel, each opened by a "Kernel Name" row: take the first
+starts=[i for i,r in enumerate(rows) if r and r[0]=='Kernel Name']
+end=starts[1] if len(starts)>1 else len(rows)
+print('kernel:',rows[0][1] if len(rows[0])>1 else '?')
+hdr=rows[1]; data=[r for r in rows[2:end] if len(r)==len(hdr)]
 ix={h:i for i,h in enumerate(hdr)}
 reasons=[h for h in hdr if h.startswith('stall_') and 'Not Issued' not in h]
 def I(x):
