@@ -145,6 +145,19 @@ int32_t rrl_ingest_wire_action(rrl_learner_t *h, const uint8_t *obs_blob, size_t
                                const uint8_t *act_blob, size_t act_len, const uint8_t *mask_blob,
                                size_t mask_len, float rew, const uint8_t *v_blob, size_t v_len,
                                const uint8_t *logp_blob, size_t logp_len, uint8_t done);
+/* gRPC wire format: one serialized proto `Trajectory` (proto/relayrl_grpc.proto:5-18) as TrainingServerGrpc::
+ * send_actions receives it (src/network/server/training_grpc.rs:585-599).  Replaces deserialize_action /
+ * grpc_trajectory_to_relayrl_trajectory (src/sys_utils/grpc_utils.rs:83-158) and everything behind them
+ * (JSON pipe, PyO3 getters, REINFORCE.receive_trajectory's per-action loop): obs/action/mask are safetensors
+ * blobs, data["logp_a"] / data["v"] are serde_json RelayRLData values (action.rs:203-218), an action with
+ * done = true is a terminal marker carrying only its reward.  Appends every action of the message. */
+int32_t rrl_ingest_grpc_trajectory(rrl_learner_t *h, const uint8_t *msg, size_t len, int64_t *n_actions);
+/* The decoder alone, host only (no GPU needed): fills caller-provided SoA f32 columns of `cap` rows in the
+ * rrl_batch_view_t convention and returns the row count; errbuf (optional) receives the failure message. */
+int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, int32_t obs_dim, int32_t act_dim,
+                                   int32_t with_baseline, float *obs, float *act, float *mask, float *rew,
+                                   float *val, float *logp, uint8_t *done, int64_t cap, int64_t *count,
+                                   char *errbuf, size_t errcap);
 
 /* ReplayBuffer.finish_path for every closed path of the epoch (replay_buffer.py:48-79) and
  * statistics_scalar over [0, ptr) (BaseReplayBuffer.py:30-53): one fused segmented reverse scan.

@@ -88,6 +88,246 @@ static float blob_at(const BlobView &b, size_t i)
     }
 }
 
+
+// ---- proto3 wire format (varint / fixed32 / length-delimited), just enough for Trajectory ---------------
+// message RelayRLAction { bytes obs = 1; bytes action = 2; bytes mask = 3; float reward = 4;
+//                         map<string, bytes> data = 5; bool done = 6; bool reward_update_flag = 7; }
+// message Trajectory    { repeated RelayRLAction actions = 1; }        (proto/relayrl_grpc.proto:5-18)
+// proto3 leaves out fields that hold their default (empty bytes, 0.0, false).
+struct Cur {
+    const uint8_t *p, *end;
+};
+static bool rd_varint(Cur &c, uint64_t &v)
+{
+    v = 0;
+    for (int shift = 0; shift < 64 && c.p < c.end; shift += 7) {
+        const uint8_t b = *c.p++;
+        v |= (uint64_t)(b & 0x7f) << shift;
+        if (!(b & 0x80)) return true;
+    }
+    return false;
+}
+static bool rd_len(Cur &c, Cur &sub)
+{
+    uint64_t n;
+    if (!rd_varint(c, n) || n > (uint64_t)(c.end - c.p)) return false;
+    sub.p = c.p, sub.end = c.p + n, c.p += n;
+    return true;
+}
+static bool skip_field(Cur &c, unsigned wire_type)
+{
+    uint64_t v;
+    Cur sub;
+    switch (wire_type) {
+        case 0: return rd_varint(c, v);
+        case 1: if (c.end - c.p < 8) return false; c.p += 8; return true;
+        case 2: return rd_len(c, sub);
+        case 5: if (c.end - c.p < 4) return false; c.p += 4; return true;
+        default: return false;  // groups are not used by this schema
+    }
+}
+
+// One value of the proto `data` map: serde_json of RelayRLData (grpc_utils.rs:45-55), an externally tagged
+// enum (action.rs:203-218): {"Tensor":{"shape":[..],"dtype":"Float","data":[<safetensors blob as byte
+// values>]}} or a scalar {"Float":x} / {"Double":x} / {"Int":n} / {"Long":n} / {"Short":n} / {"Byte":n}.
+static const char *skip_ws(const char *p, const char *end)
+{
+    while (p < end && (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r')) ++p;
+    return p;
+}
+static int32_t parse_data_value(const char *js, size_t n, std::vector<uint8_t> &scratch, float &out, const char *what, ErrBuf &err)
+{
+    const char *end = js + n;
+    const char *p = skip_ws(js, end);
+    if (p >= end || *p != '{') {
+        err.set("data['%s'] is not a JSON object", what);
+        return RRL_EFORMAT;
+    }
+    p = skip_ws(p + 1, end);
+    if (p >= end || *p != '"') {
+        err.set("data['%s']: variant tag missing", what);
+        return RRL_EFORMAT;
+    }
+    const char *tag = ++p;
+    while (p < end && *p != '"') ++p;
+    const size_t tl = (size_t)(p - tag);
+    p = skip_ws(p + 1, end);
+    if (p >= end || *p != ':') {
+        err.set("data['%s']: malformed variant", what);
+        return RRL_EFORMAT;
+    }
+    p = skip_ws(p + 1, end);
+    if (tl == 6 && !memcmp(tag, "Tensor", 6)) {
+        const char *d = find_key(p, (size_t)(end - p), "\"data\"");
+        if (d) d = skip_ws(d, end);
+        if (!d || d >= end || *d != ':') {
+            err.set("data['%s']: Tensor without a data array", what);
+            return RRL_EFORMAT;
+        }
+        d = skip_ws(d + 1, end);
+        if (d >= end || *d != '[') {
+            err.set("data['%s']: Tensor.data is not an array", what);
+            return RRL_EFORMAT;
+        }
+        ++d;
+        scratch.clear();
+        while (true) {
+            d = skip_ws(d, end);
+            if (d >= end) {
+                err.set("data['%s']: unterminated byte array", what);
+                return RRL_EFORMAT;
+            }
+            if (*d == ']') break;
+            unsigned v = 0;
+            const char *q = d;
+            while (q < end && *q >= '0' && *q <= '9') v = v * 10 + (unsigned)(*q++ - '0');
+            if (q == d || v > 255) {
+                err.set("data['%s']: byte array holds a non-byte value", what);
+                return RRL_EFORMAT;
+            }
+            scratch.push_back((uint8_t)v);
+            d = skip_ws(q, end);
+            if (d < end && *d == ',') ++d;
+        }
+        BlobView b;
+        RRL_TRY(parse_blob(scratch.data(), scratch.size(), b, err));
+        if (b.count < 1) {
+            err.set("data['%s'] is an empty tensor", what);
+            return RRL_EFORMAT;
+        }
+        out = blob_at(b, 0);
+        return RRL_OK;
+    }
+    const bool scalar = (tl == 5 && !memcmp(tag, "Float", 5)) || (tl == 6 && !memcmp(tag, "Double", 6)) ||
+                        (tl == 3 && !memcmp(tag, "Int", 3)) || (tl == 4 && !memcmp(tag, "Long", 4)) ||
+                        (tl == 5 && !memcmp(tag, "Short", 5)) || (tl == 4 && !memcmp(tag, "Byte", 4));
+    if (!scalar) {
+        err.set("data['%s']: variant %.*s carries no number", what, (int)tl, tag);
+        return RRL_EFORMAT;
+    }
+    char buf[64];
+    const size_t m = (size_t)(end - p) < sizeof(buf) - 1 ? (size_t)(end - p) : sizeof(buf) - 1;
+    memcpy(buf, p, m);
+    buf[m] = 0;
+    char *q = nullptr;
+    const double v = strtod(buf, &q);
+    if (q == buf) {
+        err.set("data['%s']: number expected", what);
+        return RRL_EFORMAT;
+    }
+    out = (float)v;
+    return RRL_OK;
+}
+
+struct HostColumns {
+    float *obs, *act, *mask, *rew, *val, *logp;
+    uint8_t *done;
+    int64_t cap;
+};
+
+// Decodes one serialized Trajectory into SoA rows (terminal markers become rows with done = 1 that carry
+// only their reward, as rrl_batch_view_t expects).
+static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int A, bool with_baseline, const HostColumns &o,
+                                      int64_t &count, ErrBuf &err)
+{
+    count = 0;
+    std::vector<uint8_t> scratch;
+    Cur top{msg, msg + len};
+    while (top.p < top.end) {
+        uint64_t key;
+        if (!rd_varint(top, key)) goto truncated;
+        if (key != ((1u << 3) | 2u)) {
+            if (!skip_field(top, (unsigned)(key & 7))) goto truncated;
+            continue;
+        }
+        Cur act;
+        if (!rd_len(top, act)) goto truncated;
+        if (count >= o.cap) {
+            err.set("trajectory holds more than the %lld rows the caller provided", (long long)o.cap);
+            return RRL_ECAPACITY;
+        }
+        {
+            Cur f_obs{nullptr, nullptr}, f_act{nullptr, nullptr}, f_mask{nullptr, nullptr}, f_logp{nullptr, nullptr}, f_v{nullptr, nullptr};
+            float rew = 0.f;
+            bool done = false;
+            while (act.p < act.end) {
+                uint64_t k;
+                if (!rd_varint(act, k)) goto truncated;
+                const unsigned field = (unsigned)(k >> 3), wt = (unsigned)(k & 7);
+                if (field >= 1 && field <= 3 && wt == 2) {
+                    Cur b;
+                    if (!rd_len(act, b)) goto truncated;
+                    (field == 1 ? f_obs : field == 2 ? f_act : f_mask) = b;
+                } else if (field == 4 && wt == 5) {
+                    if (act.end - act.p < 4) goto truncated;
+                    memcpy(&rew, act.p, 4);
+                    act.p += 4;
+                } else if (field == 5 && wt == 2) {  // one map entry: { string key = 1; bytes value = 2; }
+                    Cur e, kstr{nullptr, nullptr}, val{nullptr, nullptr};
+                    if (!rd_len(act, e)) goto truncated;
+                    while (e.p < e.end) {
+                        uint64_t ek;
+                        if (!rd_varint(e, ek)) goto truncated;
+                        if ((ek & 7) == 2 && (ek >> 3) == 1) {
+                            if (!rd_len(e, kstr)) goto truncated;
+                        } else if ((ek & 7) == 2 && (ek >> 3) == 2) {
+                            if (!rd_len(e, val)) goto truncated;
+                        } else if (!skip_field(e, (unsigned)(ek & 7))) {
+                            goto truncated;
+                        }
+                    }
+                    const size_t kl = (size_t)(kstr.end - kstr.p);
+                    if (kl == 6 && !memcmp(kstr.p, "logp_a", 6)) f_logp = val;
+                    else if (kl == 1 && kstr.p[0] == 'v') f_v = val;
+                } else if (field == 6 && wt == 0) {
+                    uint64_t b;
+                    if (!rd_varint(act, b)) goto truncated;
+                    done = b != 0;
+                } else if (!skip_field(act, wt)) {
+                    goto truncated;
+                }
+            }
+            const int64_t r = count;
+            o.rew[r] = rew, o.done[r] = done ? 1 : 0;
+            o.act[r] = 0.f, o.val[r] = 0.f, o.logp[r] = 0.f;
+            for (int i = 0; i < d; ++i) o.obs[r * d + i] = 0.f;
+            for (int i = 0; i < A; ++i) o.mask[r * A + i] = 0.f;
+            if (!done) {  // a terminal marker has obs = act = mask = data = None (agent_zmq.rs:607-608)
+                BlobView bo, ba, bm;
+                RRL_TRY(parse_blob(f_obs.p, (size_t)(f_obs.end - f_obs.p), bo, err));
+                RRL_TRY(parse_blob(f_act.p, (size_t)(f_act.end - f_act.p), ba, err));
+                RRL_TRY(parse_blob(f_mask.p, (size_t)(f_mask.end - f_mask.p), bm, err));
+                if ((int)bo.count != d || (int)bm.count != A || ba.count < 1) {
+                    err.set("action %lld: obs has %zu values (want %d), mask %zu (want %d), act %zu", (long long)r, bo.count, d,
+                            bm.count, A, ba.count);
+                    return RRL_EFORMAT;
+                }
+                for (int i = 0; i < d; ++i) o.obs[r * d + i] = blob_at(bo, i);
+                for (int i = 0; i < A; ++i) o.mask[r * A + i] = blob_at(bm, i);
+                o.act[r] = blob_at(ba, 0);
+                if (!f_logp.p) {
+                    err.set("action %lld: data['logp_a'] missing", (long long)r);
+                    return RRL_EFORMAT;
+                }
+                RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_logp.p), (size_t)(f_logp.end - f_logp.p), scratch, o.logp[r],
+                                         "logp_a", err));
+                if (with_baseline) {
+                    if (!f_v.p) {
+                        err.set("action %lld: data['v'] missing", (long long)r);
+                        return RRL_EFORMAT;
+                    }
+                    RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_v.p), (size_t)(f_v.end - f_v.p), scratch, o.val[r], "v", err));
+                }
+            }
+            ++count;
+        }
+    }
+    return RRL_OK;
+truncated:
+    err.set("serialized Trajectory is truncated or not proto3 wire format (at byte %zu of %zu)", (size_t)(top.p - msg), len);
+    return RRL_EFORMAT;
+}
+
 }  // namespace rrl
 
 using namespace rrl;
@@ -130,5 +370,41 @@ extern "C" int32_t rrl_ingest_wire_action(rrl_learner_t *h, const uint8_t *obs_b
     }
     b.obs = obs.data(), b.act = &act, b.mask = mask.data(), b.rew = &rew, b.val = &val, b.logp = &logp, b.done = &dn;
     b.count = 1, b.obs_dtype = RRL_F32, b.mask_dtype = RRL_F32;
+    return rrl_ingest_packed(h, &b);
+}
+
+extern "C" int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, int32_t obs_dim, int32_t act_dim, int32_t with_baseline,
+                                              float *obs, float *act, float *mask, float *rew, float *val, float *logp, uint8_t *done,
+                                              int64_t cap, int64_t *count, char *errbuf, size_t errcap)
+{
+    if ((!msg && len) || obs_dim < 1 || act_dim < 1 || !obs || !act || !mask || !rew || !val || !logp || !done || cap < 0 || !count)
+        return RRL_EINVAL;
+    ErrBuf err;
+    const HostColumns o{obs, act, mask, rew, val, logp, done, cap};
+    const int32_t st = decode_grpc_trajectory(msg, len, obs_dim, act_dim, with_baseline != 0, o, *count, err);
+    if (st != RRL_OK && errbuf && errcap) {
+        strncpy(errbuf, err.msg.c_str(), errcap - 1);
+        errbuf[errcap - 1] = 0;
+    }
+    return st;
+}
+
+extern "C" int32_t rrl_ingest_grpc_trajectory(rrl_learner_t *h, const uint8_t *msg, size_t len, int64_t *n_actions)
+{
+    if (!h || (!msg && len)) return RRL_EINVAL;
+    const int d = h->cfg.obs_dim, A = h->cfg.act_dim;
+    // an action costs at least 2 bytes on the wire (tag + length): that bounds the row count
+    const int64_t cap = (int64_t)(len / 2) + 1;
+    std::vector<float> obs((size_t)cap * d), mask((size_t)cap * A), act(cap), rew(cap), val(cap), logp(cap);
+    std::vector<uint8_t> done(cap);
+    const HostColumns o{obs.data(), act.data(), mask.data(), rew.data(), val.data(), logp.data(), done.data(), cap};
+    int64_t count = 0;
+    RRL_TRY(decode_grpc_trajectory(msg, len, d, A, h->cfg.with_baseline != 0, o, count, h->err));
+    if (n_actions) *n_actions = count;
+    if (count == 0) return RRL_OK;
+    rrl_batch_view_t b;
+    memset(&b, 0, sizeof b);
+    b.obs = obs.data(), b.act = act.data(), b.mask = mask.data(), b.rew = rew.data(), b.val = val.data(), b.logp = logp.data();
+    b.done = done.data(), b.count = count, b.obs_dtype = RRL_F32, b.mask_dtype = RRL_F32;
     return rrl_ingest_packed(h, &b);
 }

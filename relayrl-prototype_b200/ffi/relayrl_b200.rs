@@ -34,6 +34,7 @@ extern "C" {
     pub fn rrl_learner_create(cfg: *const RrlConfig, out: *mut *mut c_void) -> i32;
     pub fn rrl_learner_destroy(h: *mut c_void) -> i32;
     pub fn rrl_learner_stream(h: *const c_void, stream: *mut *mut c_void) -> i32;
+    pub fn rrl_ingest_grpc_trajectory(h: *mut c_void, msg: *const u8, len: usize, n_actions: *mut i64) -> i32;
     pub fn rrl_set_params(h: *mut c_void, which: i32, flat: *const f32, n: i64) -> i32;
     pub fn rrl_get_params(h: *mut c_void, which: i32, flat: *mut f32, n: i64) -> i32;
     pub fn rrl_ingest_packed(h: *mut c_void, batch: *const RrlBatchView) -> i32;

@@ -142,6 +142,13 @@ class Learner:
         (o, ol), (a, al), (m, ml), (v, vl), (lp, ll) = b(obs_blob), b(act_blob), b(mask_blob), b(v_blob), b(logp_blob)
         self._ck(self._L.rrl_ingest_wire_action(self._h, o, ol, a, al, m, ml, float(rew), v, vl, lp, ll, int(bool(done))))
 
+    def ingest_grpc_trajectory(self, msg):
+        """One serialized proto Trajectory as SendActions receives it (proto/relayrl_grpc.proto:5-18,
+        src/sys_utils/grpc_utils.rs:83-158); returns the number of actions it held."""
+        n = C.c_int64()
+        self._ck(self._L.rrl_ingest_grpc_trajectory(self._h, msg, len(msg), C.byref(n)))
+        return n.value
+
     # -- finish_path for every closed path + statistics (replay_buffer.py:48-79) ------------------
     def finish(self):
         n, e = C.c_int64(), C.c_int64()
@@ -289,3 +296,20 @@ def scan_workspace_bytes(n):
 def normalise_device(adv, n, stats, out, stream=None):
     check(_lib.lib().rrl_normalise_device(_dev_ptr(adv), n, _dev_ptr(stats), _dev_ptr(out),
                                           C.c_void_p(stream) if stream else None))
+
+
+def decode_grpc_trajectory(msg, obs_dim, act_dim, with_baseline, cap=None):
+    """Host-only decode of a serialized proto Trajectory into SoA f32 columns (rrl_batch_view_t convention:
+    a terminal marker is a row with done = 1 that carries only its reward).  Needs no GPU."""
+    L = _lib.lib()
+    cap = cap if cap is not None else len(msg) // 2 + 1
+    cols = {"obs": np.empty((cap, obs_dim), np.float32), "act": np.empty(cap, np.float32),
+            "mask": np.empty((cap, act_dim), np.float32), "rew": np.empty(cap, np.float32),
+            "val": np.empty(cap, np.float32), "logp": np.empty(cap, np.float32), "done": np.empty(cap, np.uint8)}
+    n, err = C.c_int64(), C.create_string_buffer(256)
+    st = L.rrl_decode_grpc_trajectory(msg, len(msg), obs_dim, act_dim, int(bool(with_baseline)), _ptr(cols["obs"]),
+                                      _ptr(cols["act"]), _ptr(cols["mask"]), _ptr(cols["rew"]), _ptr(cols["val"]),
+                                      _ptr(cols["logp"]), _ptr(cols["done"]), cap, C.byref(n), err, len(err))
+    if st != _lib.RRL_OK:
+        raise _lib.RelayRLB200Error(st, err.value.decode(errors="replace"))
+    return {k: v[:n.value] for k, v in cols.items()}

@@ -263,3 +263,36 @@ def test_wire_action_ingest_safetensors():
         L.ingest_wire_action(b"\x05\x00", b"", b"", 0.0, b"", b"", False)
     assert e.value.status == -6
     L.close()
+
+
+def test_grpc_trajectory_ingest_matches_golden_epoch():
+    """rrl_ingest_grpc_trajectory: the golden epoch's inputs sent as serialized proto Trajectory messages (one per
+    episode, terminal marker last, as agent_grpc.rs flushes them) give the reference's offsets and returns."""
+    from test_wire_grpc import _blob, _messages, _tensor_json
+    g = load_golden("epoch_vf_h128")
+    L, d, A, H, wb = _mk(g, iters=1)
+    p = "e0_"
+    _, Trajectory = _messages()
+    t, sent, n_in = Trajectory(), 0, len(g[p + "in_done"])
+    for i in range(n_in):
+        if g[p + "in_done"][i]:
+            t.actions.add(reward=float(g[p + "in_rew"][i]), done=True)
+            sent += L.ingest_grpc_trajectory(t.SerializeToString())
+            t = Trajectory()
+        else:
+            a = t.actions.add(obs=_blob(g[p + "in_obs"][i]), action=_blob(np.array([g[p + "in_act"][i]], np.float32)),
+                              mask=_blob(g[p + "in_mask"][i]), reward=float(g[p + "in_rew"][i]))
+            a.data["logp_a"] = _tensor_json(np.array([g[p + "in_logp"][i]], np.float32), "Float")
+            a.data["v"] = _tensor_json(np.array(g[p + "in_val"][i], np.float32), "Float")
+    if len(t.actions):
+        sent += L.ingest_grpc_trajectory(t.SerializeToString())
+    assert sent == n_in
+    n, _ = L.finish()
+    assert np.array_equal(L.offsets(), g[p + "offsets"])
+    np.testing.assert_allclose(L.returns(n), g[p + "ret_raw"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(L.advantages(n, normalised=False), g[p + "adv_raw"], rtol=1e-6, atol=1e-6)
+    from relayrl_b200 import RelayRLB200Error
+    with pytest.raises(RelayRLB200Error) as e:
+        L.ingest_grpc_trajectory(b"\x0a\x7f\x01")
+    assert e.value.status == -6
+    L.close()
