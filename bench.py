@@ -205,6 +205,64 @@ def measure_scan(cols, offsets, last_vals, n, dev, with_baseline=True, reps=20):
     return sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
 
 
+def measure_normalise(n, dev, reps=20):
+    """K3 alone (the get()-style tap): 8 B per transition, median CUDA-event time on the launching stream."""
+    import torch
+    from relayrl_b200 import normalise_device
+    adv, out = torch.randn(n, device=dev), torch.empty(n, device=dev)
+    stats = torch.tensor([0.0, 0.0, float(n), 0.25, 1.5, 0.0, 0.0, 0.0], dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i in range(3 + reps):
+        if i >= 3:
+            ev[i - 3][0].record()
+        normalise_device(adv, n, stats, out, stream=stream)
+        if i >= 3:
+            ev[i - 3][1].record()
+    torch.cuda.synchronize()
+    return sorted(a.elapsed_time(b) for a, b in ev)[reps // 2]
+
+
+def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=65536):
+    """C4: one batched PolicyWithBaseline.step per call, device-resident inputs, CUDA events on
+    the actor's own stream; beside it the oracle's step (torch CPU, all host threads) on the same shape."""
+    import torch
+    from relayrl_b200 import Actor
+    from oracle import learner_oracle as lo
+    pi, vf = lo.init_params(d, H_, A_, 11), lo.init_params(d, H_, 1, 12)
+    act = Actor(d, A_, hidden=H_, with_baseline=True, device=dev.index or 0, max_batch=batch)
+    act.set_params(0, lo.flatten(pi).numpy())
+    act.set_params(1, lo.flatten(vf).numpy())
+    g = torch.Generator(device="cpu").manual_seed(4)
+    obs_h = torch.randn(batch, d, generator=g)
+    mask_h = (torch.rand(batch, A_, generator=g) > 0.2).float()
+    mask_h[:, 0] = 1.0
+    obs, mask = obs_h.to(dev), mask_h.to(dev)
+    a_out = torch.empty(batch, dtype=torch.int64, device=dev)
+    lp, v = torch.empty(batch, device=dev), torch.empty(batch, device=dev)
+    st = torch.cuda.ExternalStream(act.stream, device=dev)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i in range(3 + reps):
+        if i >= 3:
+            ev[i - 3][0].record(st)
+        act.step_device(obs, mask, a_out, lp, v, seed=4, offset=i)
+        if i >= 3:
+            ev[i - 3][1].record(st)
+    torch.cuda.synchronize()
+    ms = sorted(a.elapsed_time(b) for a, b in ev)[reps // 2]
+    act.close()
+    torch.set_num_threads(os.cpu_count() or 1)
+    lo.actor_step(pi, vf, obs_h[:cpu_batch], mask_h[:cpu_batch])
+    t0 = time.perf_counter()
+    for _ in range(3):
+        lo.actor_step(pi, vf, obs_h[:cpu_batch], mask_h[:cpu_batch])
+    cpu_s = (time.perf_counter() - t0) / 3
+    flops = 2.0 * (d * H_ + H_ * H_ + H_ * A_) + 2.0 * (d * H_ + H_ * H_ + H_)
+    return {"workload": "C4: batch %d, d=%d, A=%d, H=%d, with baseline (policy + value + sampling per env)" % (batch, d, A_, H_),
+            "env_steps_per_s": batch / (ms * 1e-3), "ms_per_call": ms, "tflops": flops * batch / (ms * 1e-3) / 1e12,
+            "cpu_env_steps_per_s": cpu_batch / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
+
+
 def run_scan_only(args):
     import torch
     dev = torch.device("cuda", 0)
@@ -303,6 +361,15 @@ def run_ours(args):
     e2e_steps = max(1, min(args.steps, 2))
 
     scan_ms = measure_scan(cols, offsets, last_vals, n, dev)
+    extras = {}
+    if rank == 0 and world == 1 and not args.no_extras:
+        del cols                      # the learner keeps its own copy
+        torch.cuda.empty_cache()
+        norm_ms = measure_normalise(n, dev)
+        extras["roofline_normalise"] = {"kernel": "normalise_kernel (K3, get()-style tap only)", "bound": "hbm",
+                                        "achieved": 8.0 * n / (norm_ms * 1e-3) / 1e9, "unit": "GB/s", "launch_ms": norm_ms,
+                                        "bytes_per_transition": 8}
+        extras["actor"] = measure_actor(dev)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -343,6 +410,9 @@ def run_ours(args):
                          "sample": "%d transitions, full epoch with %d value iterations, %.1f s" % (args.cpu_sample, ITERS, cpu_dt)},
         "losses": {"loss_pi": s["loss_pi"], "loss_v": s["loss_v"], "entropy": s["entropy"]},
     }
+    if "roofline_normalise" in extras:
+        extras["roofline_normalise"].update(peak=hbm, frac=extras["roofline_normalise"]["achieved"] / hbm, peak_source=which)
+    line.update(extras)
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
@@ -357,6 +427,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=1 << 17)
     ap.add_argument("--ref-sample", type=int, default=1 << 17)
+    ap.add_argument("--no-extras", action="store_true", help="skip the K3 and actor (C4) side measurements")
     ap.add_argument("--scan-only", action="store_true", help="measure K2 alone (roofline_scan) and exit")
     args = ap.parse_args()
     if args.scan_only:

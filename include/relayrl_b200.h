@@ -184,6 +184,8 @@ int32_t rrl_reset_buffer(rrl_learner_t *h);
 int32_t rrl_actor_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32_t with_baseline,
                          int32_t device, int64_t max_batch, rrl_actor_t **out);
 int32_t rrl_actor_destroy(rrl_actor_t *a);
+/* The CUDA stream the actor's kernels run on (same role as rrl_learner_stream; no reference counterpart). */
+int32_t rrl_actor_stream(const rrl_actor_t *a, void **stream);
 int32_t rrl_actor_set_params(rrl_actor_t *a, int32_t which, const float *flat, int64_t n);
 /* One batched step on host buffers: act int64 [batch], logp_a f32 [batch] (= logits[i, act_i]),
  * v f32 [batch] (NULL without baseline).  Sampling: inverse-CDF on softmax(logits) with one

@@ -26,6 +26,13 @@ int32_t rrl_actor_destroy(rrl_actor_t *a)
     return RRL_OK;
 }
 
+int32_t rrl_actor_stream(const rrl_actor_t *a, void **stream)
+{
+    if (!a || !stream) return RRL_EINVAL;
+    *stream = static_cast<void *>(a->stream);
+    return RRL_OK;
+}
+
 int32_t rrl_actor_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32_t with_baseline, int32_t device,
                          int64_t max_batch, rrl_actor_t **out)
 {

@@ -78,6 +78,7 @@ SIGNATURES = {
     "rrl_actor_create": (C.c_int32, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int64,
                                      C.POINTER(_P)]),
     "rrl_actor_destroy": (C.c_int32, [_P]),
+    "rrl_actor_stream": (C.c_int32, [_P, C.POINTER(_P)]),
     "rrl_actor_set_params": (C.c_int32, [_P, C.c_int32, _P, C.c_int64]),
     "rrl_actor_step": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_uint64, C.c_uint64, _P, _P, _P, _P, _P]),
     "rrl_actor_step_device": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_uint64, C.c_uint64, _P, _P, _P, _P,

@@ -219,6 +219,12 @@ class Actor:
         except Exception:
             pass
 
+    @property
+    def stream(self):
+        st = C.c_void_p()
+        check(self._L.rrl_actor_stream(self._h, C.byref(st)), self._h, actor=True)
+        return st.value or 0
+
     def set_params(self, which, flat):
         flat = np.ascontiguousarray(flat, np.float32)
         check(self._L.rrl_actor_set_params(self._h, which, _ptr(flat), flat.size), self._h, actor=True)
