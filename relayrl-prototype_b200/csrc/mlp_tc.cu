@@ -36,7 +36,10 @@ constexpr int X_PLANE = tc::x_plane_bytes(TILE_M, TC_H);  // bytes of one bf16 p
 constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H), X_CHUNK = tc::x_chunk_bytes(TILE_M);
 // dZ2 is kept transposed: X layout of [unit][row], so that the thread that owns a unit stores 8 rows per 16 bytes
 constexpr int DZ_PLANE = tc::x_plane_bytes(TC_H, TILE_M), DZ_CHUNK = tc::x_chunk_bytes(TC_H);
-constexpr uint32_t TM_D1 = 0, TM_D2 = 64, TM_DW2 = 128, TM_ACC = 256, TM_COLS = 512;
+// TMEM columns: D1[2] (64 each; after epilogue 1 has read it, D1[k&1] is reused for planes 0 and 1 of H1^T, G3's A
+// operand), plane 2 of H1^T (32), D2 (64), dW2^T (128, one tile), ACC (128, the window's dW2^T sum)
+constexpr uint32_t TM_D1 = 0, TM_P2 = 128, TM_D2 = 160, TM_DW2 = 224, TM_ACC = 352, TM_COLS = 512;
+constexpr int NBUF = 3;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1 / prefetch)
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
 // entries deep).  17 warps are allocated as 20, i.e. 96 registers per thread: the dW2 sums therefore live in
@@ -49,22 +52,22 @@ constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (
 constexpr int OFF_W2 = 0;
 constexpr int OFF_H1 = OFF_W2 + 3 * W_PLANE;
 constexpr int OFF_DZ = OFF_H1 + 3 * X_PLANE;
-constexpr int OFF_OBS = OFF_DZ + 3 * DZ_PLANE;                // f32 [2][64][8]
-constexpr int OFF_W1 = OFF_OBS + 2 * TILE_M * TC_MAX_D * 4;   // f32 [128][8]
+constexpr int OFF_OBS = OFF_DZ + 3 * DZ_PLANE;                // f32 [NBUF][64][8]
+constexpr int OFF_W1 = OFF_OBS + NBUF * TILE_M * TC_MAX_D * 4;  // f32 [128][8]
 constexpr int OFF_B1 = OFF_W1 + TC_H * TC_MAX_D * 4;          // f32 [128]
 constexpr int OFF_B2 = OFF_B1 + TC_H * 4;
 constexpr int OFF_W3 = OFF_B2 + TC_H * 4;                     // f32 [4][128]
 constexpr int OFF_B3 = OFF_W3 + TC_MAX_OUT * TC_H * 4;        // f32 [4] (+pad)
 constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters][4][64]
-constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;      // f32 [2][64][4]
-constexpr int OFF_ROWF = OFF_MASK + 2 * TILE_M * TC_MAX_OUT * 4;       // f32 [2][3][64]: ret | adv, logp_old, act
-constexpr int OFF_HBITS = OFF_ROWF + 2 * 3 * TILE_M * 4;                  // u32 [2][128 units][2]: h1 > 0 for 64 rows
-constexpr int OFF_RED = OFF_HBITS + 2 * TC_H * 2 * 4;                  // double [16]
+constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;      // f32 [NBUF][64][4]
+constexpr int OFF_ROWF = OFF_MASK + NBUF * TILE_M * TC_MAX_OUT * 4;    // f32 [NBUF][3][64]: ret | adv, logp_old, act
+constexpr int OFF_HBITS = OFF_ROWF + NBUF * 3 * TILE_M * 4;            // u32 [NBUF][128 units][2]: h1 > 0 for 64 rows
+constexpr int OFF_RED = OFF_HBITS + NBUF * TC_H * 2 * 4;               // double [16]
 constexpr int OFF_BAR = OFF_RED + 128;                                 // 5 mbarriers + tmem base
 constexpr int TC_SMEM_BYTES = OFF_BAR + 64;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
 static_assert(TILE_M * TC_MAX_D == TC_THREADS, "one observation element per thread in the input fetch");
-static_assert(TC_H * (TC_H + 1) * 4 <= 3 * X_PLANE + 3 * DZ_PLANE, "flush staging must fit in the operand planes");
+static_assert(TC_RG * TC_H * (2 + TC_MAX_OUT + TC_MAX_D) * 4 + TILE_M * TC_MAX_OUT * 4 <= 3 * DZ_PLANE, "spill staging must fit in the dZ2 planes");
 
 // 16 values per lane: lane l returns the total over the 32 lanes for c == (l & 15)
 __device__ __forceinline__ float reduce_scatter16(float (&p)[16], int lane)
@@ -170,7 +173,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     DZ_k.lbo = DZ_CHUNK, DZ_k.sbo = 128, DZ_k.kstep = 2 * DZ_CHUNK;
     DZ_mn.sbo = DZ_CHUNK, DZ_mn.lbo = 128, DZ_mn.kstep = 256;
     constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, true),
-                       ID_G3 = idesc_bf16(128, 128, false, true);
+                       ID_G3 = idesc_bf16(128, 128, false, false);
 
     // thread-local gradient accumulators for hidden unit j over this thread's quarter of the rows.
     // dW2 row j, this warp's 32 in-units: drained from TMEM after every tile.  The tensor core adds into
@@ -184,7 +187,6 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
     double l0 = 0.0, l1 = 0.0, l2 = 0.0;
     bool first_flush = true;
-    int since_flush = 0;
     double *my_partials = a.partials + (size_t)blockIdx.x * a.n_params;
     const int64_t num_tiles = (a.n + TILE_M - 1) / TILE_M;
 
@@ -262,38 +264,135 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     auto worker_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(TC_THREADS) : "memory"); };
 
     if (warp == TC_THREADS / 32) {
-        {
         // ---- the MMA warp: follows the workers' hand-offs tile by tile ------------------------------------
-        int k = 0;
-        if ((int64_t)blockIdx.x < num_tiles) {
-            mbar_wait(go1, 0);
-            fence_after_sync();
-            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
-            mma_commit_warp(bar1);
-        }
+        // order on the tensor pipe: G1(0); then per tile k: G1(k+1) (runs under epilogue 1 of tile k), G3(k), G2(k)
         TCT_DECL;
+        auto g1 = [&](int kk) {
+            mbar_wait(go1, (uint32_t)(kk & 1));
+            TCT(3);
+            fence_after_sync();
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1 + 64 * (kk & 1), W2_k, H1_k, ID_G1, false);
+            mma_commit_warp(bar1);
+            TCT(4);
+        };
+        int k = 0;
+        if ((int64_t)blockIdx.x < num_tiles) g1(0);
         for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
+            if (tile + gridDim.x < num_tiles) g1(k + 1);
             mbar_wait(go23, (uint32_t)(k & 1));
             TCT(0);
             fence_after_sync();
-            // G3 first: it frees the H1 planes for the next tile's stage 1, which then runs under G2
-            issue_gemm_bf16x3_warp<TILE_M / 16>(tmem + TM_DW2, DZ_k, H1_mn, ID_G3, false);
+            // G3: dW2^T[in x out] = H1^T * dZ2, A = H1^T from tensor memory (planes 0, 1 in the tile's D1 buffer)
+            const uint32_t hT = tmem + TM_D1 + 64 * (k & 1);
+            issue_gemm_bf16x3_ts_warp<TILE_M / 16>(tmem + TM_DW2, hT, hT + 32, tmem + TM_P2, DZ_k, ID_G3, false);
             mma_commit_warp(bar3);
             TCT(1);
             issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_mn, ID_G2, false);
             mma_commit_warp(bar2);
             TCT(2);
-            if (tile + gridDim.x < num_tiles) {
-                mbar_wait(go1, (uint32_t)((k + 1) & 1));
-                TCT(3);
-                fence_after_sync();
-                issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1, W2_k, H1_k, ID_G1, false);
-                mma_commit_warp(bar1);
-                TCT(4);
-            }
-        }
         }
     } else {
+
+    // ---- epilogue 2 of tile kk (inputs in buffer b3): dz1 = D2 [h1 > 0]; dW1, db1 ------------------------------
+    auto epilogue2 = [&](int kk, int b3) {
+        mbar_wait(bar2, (uint32_t)(kk & 1));
+        fence_after_sync();
+        float dh[TC_RPT];
+        tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
+        const uint32_t hb = hbits_s[(b3 * TC_H + j) * 2 + (rq >> 1)] >> (TC_RPT * (rq & 1));
+        const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
+        float dbl = 0.f;
+#pragma unroll
+        for (int c = 0; c < TC_RPT; ++c) {
+            const int m = TC_RPT * rq + c;
+            const float dz1 = ((hb >> c) & 1u) ? dh[c] : 0.f;
+            dbl += dz1;
+#pragma unroll
+            for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
+                if (4 * i4 < d) {
+                    const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
+                    dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
+                    dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
+                    dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
+                    dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
+                }
+            }
+        }
+        db1acc += dbl;
+    };
+    // ---- drain tile kk's dW2^T (TMEM lane = in unit j, this warp's 32 out units) into the window sum in TMEM ----
+    auto drain = [&](int kk, bool first_in_window) {
+        mbar_wait(bar3, (uint32_t)(kk & 1));
+        fence_after_sync();
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+            float v[16], s[16];
+            tmem_ld16(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v);
+            if (!first_in_window) {
+                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, s);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) v[c] += s[c];
+            }
+            tmem_st16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
+        }
+    };
+    // ---- spill the f32 window into the CTA's float64 partials (staging in the dZ2 planes, idle at that point) ----
+    auto spill = [&]() {
+        // each float64 partial is owned by one thread: the first window stores, later windows add with fire-and-
+        // forget reductions (no load latency on the path; one thread per address => fixed order).  dW2^T sits in
+        // TMEM with lane = in unit: for a fixed out unit the 32 lanes of a warp hit 32 consecutive doubles.
+        auto put = [&](int64_t p, float v) {
+            if (first_flush)
+                __stcg(my_partials + p, (double)v);
+            else
+                atomicAdd(my_partials + p, (double)v);
+        };
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+            float v[16];
+            tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
+#pragma unroll
+            for (int c = 0; c < 16; ++c) put(nd.oW2() + (int64_t)(32 * rq + 16 * hf + c) * TC_H + j, v[c]);
+        }
+        // per-unit accumulators: the row groups meet in shared memory
+        float *stage = reinterpret_cast<float *>(dz_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
+        constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
+        float *mine = stage + (rq * TC_H + j) * S;
+        mine[0] = db1acc, mine[1] = db2acc;
+#pragma unroll
+        for (int i = 0; i < TC_MAX_OUT; ++i) mine[2 + i] = dW3acc[i];
+#pragma unroll
+        for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
+        float *stage3 = stage + TC_RG * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
+        if (q == 0 && lane < TC_RPT)
+#pragma unroll
+            for (int i = 0; i < TC_MAX_OUT; ++i) stage3[(TC_RPT * rq + lane) * TC_MAX_OUT + i] = db3acc[i];
+        worker_sync();
+        if (tid < TC_H) {
+            auto tot = [&](int kk) {
+                float t = 0.f;
+#pragma unroll
+                for (int g_ = 0; g_ < TC_RG; ++g_) t += stage[(g_ * TC_H + tid) * S + kk];
+                return t;
+            };
+            put(nd.ob1() + tid, tot(0));
+            put(nd.ob2() + tid, tot(1));
+            for (int o_ = 0; o_ < out; ++o_) put(nd.oW3() + (int64_t)o_ * TC_H + tid, tot(2 + o_));
+            for (int i = 0; i < d; ++i) put(nd.oW1() + (int64_t)tid * d + i, tot(2 + TC_MAX_OUT + i));
+        }
+        if (tid < out) {
+            float s = 0.f;
+            for (int m = 0; m < TILE_M; ++m) s += stage3[m * TC_MAX_OUT + tid];
+            put(nd.ob3() + tid, s);
+        }
+        db1acc = 0.f, db2acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
+#pragma unroll
+        for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
+        first_flush = false;
+        worker_sync();  // the staging area is read: epilogue 1 may write the dZ2 planes again
+    };
 
     // ---- pipeline prologue: inputs and H1 of the first tile, G1 in flight ---------------------------------
     if ((int64_t)blockIdx.x < num_tiles) {
@@ -305,28 +404,49 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         fence_before_sync();
         worker_sync();
         if (tid == 0) mbar_arrive(go1);
+        if ((int64_t)blockIdx.x + gridDim.x < num_tiles) fetch_async((int64_t)blockIdx.x + gridDim.x, 1);
     }
 
     int k = 0;
     TCT_DECL;
     for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
-        const int b = k & 1;
-        const uint32_t parity = (uint32_t)(k & 1);
-        const int64_t next = tile + gridDim.x;
+        const int b3 = k % NBUF, nb3 = (k + 1) % NBUF, pb3 = (k + 2) % NBUF;  // this, next, previous tile's inputs
+        const int64_t next = tile + gridDim.x, next2 = next + gridDim.x;
         const bool has_next = next < num_tiles;
-        ++since_flush;
-        const bool flush_now = since_flush == FLUSH_TILES || !has_next;
-        const float *rf = rowf_s + b * 3 * TILE_M;
+        const float *rf = rowf_s + b3 * 3 * TILE_M;
         const int rows_k = (int)min((int64_t)TILE_M, a.n - tile * TILE_M);
 
-        mbar_wait(bar1, parity);
+        mbar_wait(bar1, (uint32_t)(k & 1));  // G1(k) retired: D1[k & 1] is ready and the H1 planes are free
         TCT(5);
         fence_after_sync();
 
-        // ---- epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) -------------------------------------
+        // ---- [A] stage 1 of the next tile; its G1 then runs under everything below --------------------------
+        if (has_next) {
+            inputs_landed();
+            fence_before_sync();
+            worker_sync();
+            stage1(nb3);
+            fence_smem_to_async();
+            fence_before_sync();
+            worker_sync();
+            if (tid == 0) mbar_arrive(go1);
+        }
+        TCT(8);
+
+        // ---- [D] the previous tile's tail: its G3 and G2 retired long ago -----------------------------------------
+        if (k > 0) {
+            drain(k - 1, (k - 1) % FLUSH_TILES == 0);
+            TCT(7);
+            epilogue2(k - 1, pb3);
+            TCT(10);
+            if (k % FLUSH_TILES == 0) spill();
+            TCT(11);
+        }
+
+        // ---- [B] epilogue 1 (thread = hidden unit j, rows 16*rq .. 16*rq+15) ---------------------------------------
         {
             float h2[TC_RPT];
-            tmem_ld16(tmem_lane + TM_D1 + TC_RPT * rq, h2);
+            tmem_ld16(tmem_lane + TM_D1 + 64 * (k & 1) + TC_RPT * rq, h2);
             const float b2 = b2_s[j];
 #pragma unroll
             for (int c = 0; c < TC_RPT; ++c) h2[c] = fmaxf(h2[c] + b2, 0.f);
@@ -338,8 +458,43 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 const float tot = reduce_scatter16(p, lane);  // row 16*rq + (lane & 15), summed over this warp's 32 units
                 if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
-            worker_sync();  // (also: every warp has left the previous tile, whose input buffers are free again)
-            if (has_next) fetch_async(next, b ^ 1);
+            fence_before_sync();
+            worker_sync();  // (also: every warp has read D1[k & 1] and has left the previous tile's input buffers)
+            fence_after_sync();
+            if (next2 < num_tiles) fetch_async(next2, pb3);
+            // H1^T of this tile -> tensor memory (G3's A operand): recomputed from obs with thread = hidden unit, two rows
+            // per 32-bit column; planes 0 and 1 go where D1[k & 1] was, plane 2 has its own 32 columns
+            {
+                const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
+                float4 w1r[TC_MAX_D / 4];
+#pragma unroll
+                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
+                const float b1 = b1_s[j];
+                uint32_t hk[3][TC_RPT / 2];
+#pragma unroll
+                for (int c = 0; c < TC_RPT; c += 2) {
+                    Trunc3 s2[2];
+#pragma unroll
+                    for (int t = 0; t < 2; ++t) {
+                        const int m = TC_RPT * rq + c + t;
+                        float acc = b1;
+#pragma unroll
+                        for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
+                            if (4 * i4 < d) {  // same operation order as stage 1: the two copies of H1 are identical
+                                const float4 x = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
+                                acc = fmaf(x.x, w1r[i4].x, acc), acc = fmaf(x.y, w1r[i4].y, acc);
+                                acc = fmaf(x.z, w1r[i4].z, acc), acc = fmaf(x.w, w1r[i4].w, acc);
+                            }
+                        s2[t] = trunc3(fmaxf(acc, 0.f));
+                    }
+                    hk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), hk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2),
+                    hk[2][c >> 1] = pack_hi16(s2[0].t3, s2[1].t3);
+                }
+                const uint32_t hT = tmem_lane + TM_D1 + 64 * (k & 1) + (TC_RPT / 2) * rq;
+                tmem_st8(hT, hk[0]);
+                tmem_st8(hT + 32, hk[1]);
+                tmem_st8(tmem_lane + TM_P2 + (TC_RPT / 2) * rq, hk[2]);
+            }
             // per-row loss and dhead: lane l of every warp works out row 16*rq + (l & 15); the four unit
             // quarters do it redundantly (it is a handful of instructions), only q == 0 keeps the sums
             float g_lane;
@@ -362,7 +517,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                         if (keeper) db3acc[0] += g_lane;
                     }
                 } else {
-                    const float *mk = mask_s + b * TILE_M * TC_MAX_OUT;
+                    const float *mk = mask_s + b3 * TILE_M * TC_MAX_OUT;
                     float mx = -INFINITY;
 #pragma unroll
                     for (int o_ = 0; o_ < TC_MAX_OUT; ++o_)
@@ -431,154 +586,14 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         fence_smem_to_async();
         fence_before_sync();
         worker_sync();
-
         if (tid == 0) mbar_arrive(go23);  // the MMA warp issues G3, then G2
         TCT(6);
-
-        // ---- drain this tile's dW2 (TMEM lane = out unit j, this warp's quarter of the in units) -------------
-        mbar_wait(bar3, parity);
-        TCT(7);
-        fence_after_sync();
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {
-            float v[16], s[16];
-            tmem_ld16(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v);
-            if (since_flush > 1) {
-                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, s);
-#pragma unroll
-                for (int c = 0; c < 16; ++c) v[c] += s[c];
-            }
-            tmem_st16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
-        }
-
-        // ---- stage 1 of the next tile under G2; its G1 under epilogue 2 ------------------------------------
-        const bool early_next = has_next && !flush_now;
-        if (has_next) inputs_landed();
-        if (early_next) {
-            fence_before_sync();
-            worker_sync();  // the next inputs are visible; every warp saw G3 retire (H1 planes are free)
-            stage1(b ^ 1);
-            fence_smem_to_async();
-            fence_before_sync();
-            worker_sync();
-            if (tid == 0) mbar_arrive(go1);
-        }
-        TCT(8);
-
-        // ---- epilogue 2: dz1 = D2 [h1 > 0]; dW1, db1 -------------------------------------------------------
-        mbar_wait(bar2, parity);
-        TCT(9);
-        fence_after_sync();
-        {
-            float dh[TC_RPT];
-            tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
-            const uint32_t hb = hbits_s[(b * TC_H + j) * 2 + (rq >> 1)] >> (TC_RPT * (rq & 1));
-            const float *ob = obs_s + b * TILE_M * TC_MAX_D;
-            float dbl = 0.f;
-#pragma unroll
-            for (int c = 0; c < TC_RPT; ++c) {
-                const int m = TC_RPT * rq + c;
-                const float dz1 = ((hb >> c) & 1u) ? dh[c] : 0.f;
-                dbl += dz1;
-#pragma unroll
-                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
-                    if (4 * i4 < d) {
-                        const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
-                        dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
-                        dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
-                        dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
-                        dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
-                    }
-                }
-            }
-            db1acc += dbl;
-        }
-
-        TCT(10);
-        // ---- spill the f32 window into the CTA's float64 partials -------------------------------------------
-        if (flush_now) {
-            since_flush = 0;
-            auto put = [&](int64_t p, float v) {
-                if (first_flush)
-                    my_partials[p] = (double)v;
-                else
-                    atomicAdd(my_partials + p, (double)v);
-            };
-            // dW2 (128 x 128 f32) is transposed through shared memory (no GEMM is in flight: the H1 and dz
-            // planes are idle, 97 KB) so that the float64 read-modify-write in global memory is fully coalesced
-            float *w2stage = reinterpret_cast<float *>(h1_p);  // [128][129]
-            worker_sync();  // every warp has seen G2 and G3 retire
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf) {
-                float v[16];
-                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
-#pragma unroll
-                for (int c = 0; c < 16; ++c) w2stage[j * 129 + 32 * rq + 16 * hf + c] = v[c];
-            }
-            worker_sync();
-            {
-                // each float64 partial is owned by one thread: the first window stores, later windows add with
-                // fire-and-forget reductions (no load latency on the path; one thread per address => fixed order)
-                double *dst = my_partials + nd.oW2();
-#pragma unroll 8
-                for (int e = 0; e < TC_H * TC_H / TC_THREADS; ++e) {
-                    const int idx = tid + e * TC_THREADS;
-                    const double w = (double)w2stage[(idx >> 7) * 129 + (idx & 127)];
-                    if (first_flush)
-                        __stcg(dst + idx, w);
-                    else
-                        atomicAdd(dst + idx, w);
-                }
-            }
-            worker_sync();
-            // per-unit accumulators: the row groups meet in shared memory
-            float *stage = reinterpret_cast<float *>(h1_p);  // [TC_RG][128][S], S = 2 + MAX_OUT + MAX_D
-            constexpr int S = 2 + TC_MAX_OUT + TC_MAX_D;
-            float *mine = stage + (rq * TC_H + j) * S;
-            mine[0] = db1acc, mine[1] = db2acc;
-#pragma unroll
-            for (int i = 0; i < TC_MAX_OUT; ++i) mine[2 + i] = dW3acc[i];
-#pragma unroll
-            for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
-            float *stage3 = stage + TC_RG * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
-            if (q == 0 && lane < TC_RPT)
-#pragma unroll
-                for (int i = 0; i < TC_MAX_OUT; ++i) stage3[(TC_RPT * rq + lane) * TC_MAX_OUT + i] = db3acc[i];
-            worker_sync();
-            if (tid < TC_H) {
-                auto tot = [&](int kk) {
-                    float t = 0.f;
-#pragma unroll
-                    for (int g_ = 0; g_ < TC_RG; ++g_) t += stage[(g_ * TC_H + tid) * S + kk];
-                    return t;
-                };
-                put(nd.ob1() + tid, tot(0));
-                put(nd.ob2() + tid, tot(1));
-                for (int o_ = 0; o_ < out; ++o_) put(nd.oW3() + (int64_t)o_ * TC_H + tid, tot(2 + o_));
-                for (int i = 0; i < d; ++i) put(nd.oW1() + (int64_t)tid * d + i, tot(2 + TC_MAX_OUT + i));
-            }
-            if (tid < out) {
-                float s = 0.f;
-                for (int m = 0; m < TILE_M; ++m) s += stage3[m * TC_MAX_OUT + tid];
-                put(nd.ob3() + tid, s);
-            }
-            db1acc = 0.f, db2acc = 0.f;
-#pragma unroll
-            for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
-#pragma unroll
-            for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
-            first_flush = false;
-            if (has_next) {  // restart the pipeline: the staging area becomes the H1 planes again
-                fence_before_sync();
-                worker_sync();
-                stage1(b ^ 1);
-                fence_smem_to_async();
-                fence_before_sync();
-                worker_sync();
-                if (tid == 0) mbar_arrive(go1);
-            }
-        }
-        TCT(11);
+    }
+    // ---- pipeline tail: the last tile's drain, epilogue 2 and the final spill ------------------------------------
+    if (k > 0) {
+        drain(k - 1, (k - 1) % FLUSH_TILES == 0);
+        epilogue2(k - 1, (k - 1) % NBUF);
+        spill();
     }
     }  // worker warps
 

@@ -143,6 +143,20 @@ __device__ __forceinline__ void mma_bf16_elect(uint32_t d_tmem, uint64_t a_desc,
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
         : "memory");
 }
+// A operand taken from tensor memory (lane = row of A, 32-bit column = two consecutive K elements, the lower K
+// index in the lower half-word); B from shared memory as usual.
+__device__ __forceinline__ void mma_bf16_ts_elect(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, bool accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"((uint32_t)accumulate)
+        : "memory");
+}
 __device__ __forceinline__ bool elect_one()
 {
     uint32_t pred;
@@ -221,6 +235,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// registers -> TMEM: 32 lanes x 8 consecutive 32-bit columns (thread = lane)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
 // registers -> TMEM: 32 lanes x 16 consecutive 32-bit columns (thread = lane)
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16])
 {
@@ -270,6 +292,23 @@ __device__ __forceinline__ void issue_gemm_bf16x3_warp(uint32_t d_tmem, const Op
         for (int s = 0; s < KSTEPS; ++s) {
             const uint32_t oa = (pa[t] * A.plane_bytes + s * A.kstep) >> 4, ob = (pb[t] * B.plane_bytes + s * B.kstep) >> 4;
             mma_bf16_elect(d_tmem, da + oa, db + ob, idesc, accumulate_into_d || t > 0 || s > 0);
+        }
+    }
+}
+// A from TMEM: the three planes of A start at columns a0, a1, a2; a K step (16 elements) is 8 columns
+template <int KSTEPS>
+__device__ __forceinline__ void issue_gemm_bf16x3_ts_warp(uint32_t d_tmem, uint32_t a0, uint32_t a1, uint32_t a2, const OperandDesc &B,
+                                                          uint32_t idesc, bool accumulate_into_d)
+{
+    const uint64_t db = smem_desc(B.base, B.lbo, B.sbo);
+    const int pa[6] = {0, 1, 2, 0, 1, 0}, pb[6] = {2, 1, 0, 1, 0, 0};
+#pragma unroll
+    for (int t = 0; t < 6; ++t) {
+        const uint32_t a = pa[t] == 0 ? a0 : pa[t] == 1 ? a1 : a2;
+#pragma unroll
+        for (int s = 0; s < KSTEPS; ++s) {
+            const uint32_t ob = (pb[t] * B.plane_bytes + s * B.kstep) >> 4;
+            mma_bf16_ts_elect(d_tmem, a + 8 * s, db + ob, idesc, accumulate_into_d || t > 0 || s > 0);
         }
     }
 }

@@ -14,6 +14,8 @@ using namespace tc;
 // mode 2: D[128 x 128] = A[64 x 128]^T * B[64 x 128]       (A MN-major, B MN-major)   -- weight-gradient GEMM
 // mode 3: D[128 x 128] = A[128 x 0:64] * B[64 x 128]       (A K-major,  B MN-major)   -- weight-gradient GEMM with
 //                                                                                         the transposed dZ2 planes
+// mode 4: D[128 x 128] = A[64 x 128]^T * B[128 x 0:64]^T   (A^T in TENSOR MEMORY, B K-major)  -- weight-gradient GEMM
+//                                                                                            with H1^T kept in TMEM
 // All inputs row-major fp32 [rows][128] in global memory.
 __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const float *__restrict__ A,
                                                               const float *__restrict__ B, float *__restrict__ D)
@@ -22,7 +24,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int RA = mode == 2 ? 64 : 128, RB = 64;
+    const int RA = (mode == 2 || mode == 4) ? 64 : 128, RB = mode == 4 ? 128 : 64;
     const uint32_t planeA = x_plane_bytes(RA, 128), planeB = x_plane_bytes(RB, 128);
     unsigned char *sa = smem, *sb = smem + 3 * planeA;
 
@@ -42,7 +44,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
         *reinterpret_cast<__nv_bfloat16 *>(sb + planeB + o) = s.p2;
         *reinterpret_cast<__nv_bfloat16 *>(sb + 2 * planeB + o) = s.p3;
     }
-    if (warp == 0) tmem_alloc(&tmem_base_s, 128);
+    if (warp == 0) tmem_alloc(&tmem_base_s, 256);
     if (tid == 0) {
         mbar_init(&bar, 1);
         mbar_fence_init();
@@ -54,7 +56,29 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
     const uint32_t tmem = tmem_base_s;
 
     const int N = mode >= 2 ? 128 : 64;
-    if (tid == 0) {
+    if (mode == 4) {
+        // thread = lane v: A^T[v][k = row], two rows per 32-bit column, three planes of 32 columns at 128, 160, 192
+#pragma unroll 1
+        for (int c0 = 0; c0 < 32; c0 += 8) {
+            uint32_t w[3][8];
+            for (int c = 0; c < 8; ++c) {
+                const Trunc3 lo = trunc3(A[(size_t)(2 * (c0 + c)) * 128 + tid]), hi = trunc3(A[(size_t)(2 * (c0 + c) + 1) * 128 + tid]);
+                w[0][c] = pack_hi16(lo.t1, hi.t1), w[1][c] = pack_hi16(lo.t2, hi.t2), w[2][c] = pack_hi16(lo.t3, hi.t3);
+            }
+            for (int pl = 0; pl < 3; ++pl) tmem_st8(tmem + ((uint32_t)(32 * warp) << 16) + 128 + 32 * pl + c0, w[pl]);
+        }
+        fence_before_sync();
+        __syncthreads();
+        fence_after_sync();
+        if (warp == 0) {
+            OperandDesc b;
+            b.base = smem_u32(sb), b.plane_bytes = planeB;
+            b.lbo = x_chunk_bytes(RB), b.sbo = 128, b.kstep = 2 * x_chunk_bytes(RB);
+            issue_gemm_bf16x3_ts_warp<4>(tmem, tmem + 128, tmem + 160, tmem + 192, b, idesc_bf16(128, 128, false, false), false);
+            mma_commit_warp(&bar);
+        }
+    }
+    if (mode != 4 && tid == 0) {
         OperandDesc a, b;
         a.base = smem_u32(sa), a.plane_bytes = planeA;
         b.base = smem_u32(sb), b.plane_bytes = planeB;
@@ -92,7 +116,7 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tmem, 128);
+    if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 }  // namespace
@@ -101,8 +125,8 @@ __global__ void __launch_bounds__(128, 1) tc_gemm_test_kernel(int mode, const fl
 extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *B, float *D, void *stream)
 {
     using namespace rrl;
-    if (mode < 0 || mode > 3 || !A || !B || !D) return RRL_EINVAL;
-    const size_t smem = 3 * (size_t)rrl::tc::x_plane_bytes(mode == 2 ? 64 : 128, 128) + 3 * (size_t)rrl::tc::x_plane_bytes(64, 128);
+    if (mode < 0 || mode > 4 || !A || !B || !D) return RRL_EINVAL;
+    const size_t smem = 3 * (size_t)rrl::tc::x_plane_bytes((mode == 2 || mode == 4) ? 64 : 128, 128) + 3 * (size_t)rrl::tc::x_plane_bytes(mode == 4 ? 128 : 64, 128);
     if (cudaFuncSetAttribute(tc_gemm_test_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
     tc_gemm_test_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(mode, A, B, D);
     return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;

@@ -9,7 +9,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
 def test_tc_gemm_bf16x3(mode):
     import torch
     from relayrl_b200 import _lib
@@ -17,13 +17,15 @@ def test_tc_gemm_bf16x3(mode):
     fn = L.rrl_debug_tc_gemm
     fn.restype, fn.argtypes = C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     rng = np.random.default_rng(mode)
-    ra = 64 if mode == 2 else 128
+    ra, rb = (64 if mode in (2, 4) else 128), (128 if mode == 4 else 64)
     A = (rng.standard_normal((ra, 128)) * np.exp(rng.uniform(-3, 3, (ra, 128)))).astype(np.float32)
-    B = (rng.standard_normal((64, 128)) * np.exp(rng.uniform(-3, 3, (64, 128)))).astype(np.float32)
+    B = (rng.standard_normal((rb, 128)) * np.exp(rng.uniform(-3, 3, (rb, 128)))).astype(np.float32)
     A64, B64 = A.astype(np.float64), B.astype(np.float64)
     def prod(a, b):
         if mode == 3:  # only the first 64 features of A take part
             return a[:, :64] @ b
+        if mode == 4:  # A^T from tensor memory; only the first 64 features of B take part
+            return a.T @ b[:, :64].T
         return a @ b.T if mode == 0 else a.T @ b.T if mode == 1 else a.T @ b
     ref, mag = prod(A64, B64), prod(np.abs(A64), np.abs(B64))
     dev = torch.device("cuda:0")
