@@ -61,8 +61,7 @@ constexpr int OFF_B3 = OFF_W3 + TC_MAX_OUT * TC_H * 4;        // f32 [4] (+pad)
 constexpr int OFF_VPART = OFF_B3 + 64;                        // f32 [4 quarters][4][64]
 constexpr int OFF_MASK = OFF_VPART + 4 * TC_MAX_OUT * TILE_M * 4;      // f32 [NBUF][64][4]
 constexpr int OFF_ROWF = OFF_MASK + NBUF * TILE_M * TC_MAX_OUT * 4;    // f32 [NBUF][3][64]: ret | adv, logp_old, act
-constexpr int OFF_HBITS = OFF_ROWF + NBUF * 3 * TILE_M * 4;            // u32 [NBUF][128 units][2]: h1 > 0 for 64 rows
-constexpr int OFF_RED = OFF_HBITS + NBUF * TC_H * 2 * 4;               // double [16]
+constexpr int OFF_RED = OFF_ROWF + NBUF * 3 * TILE_M * 4;              // double [16]
 constexpr int OFF_BAR = OFF_RED + 128;                                 // 5 mbarriers + tmem base
 constexpr int TC_SMEM_BYTES = OFF_BAR + 64;
 static_assert(TC_SMEM_BYTES <= 227 * 1024, "tensor-core learner kernel exceeds shared memory");
@@ -111,7 +110,6 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     float *w3_s = reinterpret_cast<float *>(smem + OFF_W3), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
     float *vpart_s = reinterpret_cast<float *>(smem + OFF_VPART), *mask_s = reinterpret_cast<float *>(smem + OFF_MASK);
     float *rowf_s = reinterpret_cast<float *>(smem + OFF_ROWF);
-    uint32_t *hbits_s = reinterpret_cast<uint32_t *>(smem + OFF_HBITS);
     double *red_s = reinterpret_cast<double *>(smem + OFF_RED);
     // bar1/2/3: G1/G2/G3 retired (tensor core -> workers); go1/go23: operands staged (workers -> MMA warp)
     uint64_t *bar1 = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *bar2 = bar1 + 1, *bar3 = bar1 + 2, *go1 = bar1 + 3, *go23 = bar1 + 4;
@@ -222,7 +220,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     auto inputs_landed = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
-    // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units) + the relu bit mask
+    // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units)
     auto stage1 = [&](int b) {
         const float *ob = obs_s + b * TILE_M * TC_MAX_D;
 #pragma unroll 1
@@ -232,14 +230,16 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
             for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
                 x[i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&ob[r * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
-            uint32_t w1[4], w2[4], w3[4], bits = 0u;
+            const float4 ba = *reinterpret_cast<const float4 *>(&b1_s[8 * ch]), bb = *reinterpret_cast<const float4 *>(&b1_s[8 * ch + 4]);
+            const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+            uint32_t w1[4], w2[4], w3[4];
 #pragma unroll
             for (int e = 0; e < 8; e += 2) {
                 Trunc3 s[2];
 #pragma unroll
                 for (int t = 0; t < 2; ++t) {
                     const int u = 8 * ch + e + t;
-                    float acc = b1_s[u];
+                    float acc = bias[e + t];
 #pragma unroll
                     for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
                         if (4 * i4 < d) {  // W1 rows are zero padded
@@ -247,8 +247,6 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                             acc = fmaf(x[i4].x, w.x, acc), acc = fmaf(x[i4].y, w.y, acc);
                             acc = fmaf(x[i4].z, w.z, acc), acc = fmaf(x[i4].w, w.w, acc);
                         }
-                    const unsigned bal = __ballot_sync(0xffffffffu, acc > 0.f);  // 32 rows of unit u
-                    if (lane == e + t) bits = bal;
                     s[t] = trunc3(fmaxf(acc, 0.f));
                 }
                 w1[e >> 1] = pack_hi16(s[0].t1, s[1].t1), w2[e >> 1] = pack_hi16(s[0].t2, s[1].t2), w3[e >> 1] = pack_hi16(s[0].t3, s[1].t3);
@@ -257,7 +255,6 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
             *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
             *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(w3[0], w3[1], w3[2], w3[3]);
-            if (lane < 8) hbits_s[(b * TC_H + 8 * ch + lane) * 2 + ((r >> 5) & 1)] = bits;
         }
     };
     // the 16 worker warps meet at a named barrier; the MMA warp never joins it
@@ -293,13 +290,14 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         }
     } else {
 
+    uint32_t hb_carry = 0u;
     // ---- epilogue 2 of tile kk (inputs in buffer b3): dz1 = D2 [h1 > 0]; dW1, db1 ------------------------------
     auto epilogue2 = [&](int kk, int b3) {
         mbar_wait(bar2, (uint32_t)(kk & 1));
         fence_after_sync();
         float dh[TC_RPT];
         tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
-        const uint32_t hb = hbits_s[(b3 * TC_H + j) * 2 + (rq >> 1)] >> (TC_RPT * (rq & 1));
+        const uint32_t hb = hb_carry;  // bit c: h1 > 0 for row 16 rq + c of that tile (set by this thread in its epilogue 1)
         const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
         float dbl = 0.f;
 #pragma unroll
@@ -470,7 +468,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
                 for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
                 const float b1 = b1_s[j];
-                uint32_t hk[3][TC_RPT / 2];
+                uint32_t hk[3][TC_RPT / 2], hbits = 0u;
 #pragma unroll
                 for (int c = 0; c < TC_RPT; c += 2) {
                     Trunc3 s2[2];
@@ -485,6 +483,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                                 acc = fmaf(x.x, w1r[i4].x, acc), acc = fmaf(x.y, w1r[i4].y, acc);
                                 acc = fmaf(x.z, w1r[i4].z, acc), acc = fmaf(x.w, w1r[i4].w, acc);
                             }
+                        hbits |= (acc > 0.f ? 1u : 0u) << (c + t);
                         s2[t] = trunc3(fmaxf(acc, 0.f));
                     }
                     hk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), hk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2),
@@ -494,6 +493,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 tmem_st8(hT, hk[0]);
                 tmem_st8(hT + 32, hk[1]);
                 tmem_st8(tmem_lane + TM_P2 + (TC_RPT / 2) * rq, hk[2]);
+                hb_carry = hbits;  // the relu mask epilogue 2 needs one tile later: same thread, stays in a register
             }
             // per-row loss and dhead: lane l of every warp works out row 16*rq + (l & 15); the four unit
             // quarters do it redundantly (it is a handful of instructions), only q == 0 keeps the sums

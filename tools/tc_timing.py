@@ -7,14 +7,14 @@ lib = _lib.lib()
 f = lib.rrl_debug_tc_timing
 f.argtypes = [ctypes.c_void_p, ctypes.c_int32]; f.restype = ctypes.c_int32
 import bench
-sys.argv = ["bench.py", "--transitions", "1048576", "--steps", "1", "--warmup", "1", "--cpu-sample", "2048"]
+sys.argv = ["bench.py", "--transitions", "1048576", "--steps", "1", "--warmup", "1", "--cpu-sample", "2048", "--no-extras"]
 out = (ctypes.c_ulonglong * 16)()
 f(None, 1)
 bench.main()
 torch.cuda.synchronize()
 f(out, 0)
 v = list(out)
-names = ["mma:wait go23", "mma:G3 issue", "mma:G2 issue", "mma:wait go1", "mma:G1 issue", "wrk:wait bar1", "wrk:epi1->go23", "wrk:wait bar3", "wrk:drain+stage1", "wrk:wait bar2", "wrk:epi2", "wrk:flush"]
+names = ["mma:wait go23", "mma:G3 issue", "mma:G2 issue", "mma:wait go1", "mma:G1 issue", "wrk:wait bar1", "wrk:epi1+H1T->go23", "wrk:wait bar3+drain", "wrk:stage1(next)", "wrk:(unused)", "wrk:wait bar2+epi2", "wrk:spill"]
 m = sum(v[:5]); w = sum(v[5:12])
 for i, (n, x) in enumerate(zip(names, v)):
     tot = m if i < 5 else w
