@@ -218,6 +218,10 @@ def test_plugin_class_end_to_end(tmp_path):
         assert algo.receive_trajectory(DuckTrajectory(acts)) is True
         np.testing.assert_allclose(algo.last_stats["loss_pi"], float(g[p + "LossPi"]), rtol=1e-5, atol=1e-7)
         assert_weights_close(algo.learner.get_params(1), g[p + "v"], 1e-3)
+        algo.save()  # every epoch: the ScriptModule is scripted once and must still carry the fresh weights
+        sd = torch.jit.load(str(model)).state_dict()
+        assert np.array_equal(sd["policy.pi_network.0.weight"].numpy().reshape(-1), algo.learner.get_params(0)[:4 * 128])
+        assert np.array_equal(sd["baseline.v_network.4.bias"].numpy().reshape(-1), algo.learner.get_params(1)[-1:])
     algo.save()
     m = torch.jit.load(str(model))
     assert m.get_input_dim() == 4 and m.get_output_dim() == 2
