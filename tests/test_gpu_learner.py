@@ -300,3 +300,51 @@ def test_grpc_trajectory_ingest_matches_golden_epoch():
         L.ingest_grpc_trajectory(b"\x0a\x7f\x01")
     assert e.value.status == -6
     L.close()
+
+
+@pytest.mark.parametrize("n,d,A", [(64 * 148 * 17 + 5, 4, 2), (64 * 148 * 33 + 63, 8, 4), (130, 1, 1 + 2), (63, 3, 2)])
+def test_tc_gradients_many_tiles_vs_float64_autograd(n, d, A):
+    """The tensor-core kernel's pipeline at scale: more than 16 (and 32) tiles per CTA, so the f32 window spills
+    into the float64 partials inside the loop, ragged last tiles, and the deferred tail of the last tile.
+    Gradients and losses of one policy and one value pass against the oracle run in float64 (autograd)."""
+    rng = np.random.default_rng(n)
+    H = 128
+    lens = []
+    while sum(lens) < n:
+        lens.append(int(rng.integers(1, 3000)))
+    lens[-1] -= sum(lens) - n
+    done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
+    m = len(done)
+    obs = rng.standard_normal((m, d)).astype(np.float32)
+    act = rng.integers(0, A, m).astype(np.float32)
+    mask = np.ones((m, A), np.float32)
+    if A > 1:
+        off = rng.integers(0, A, m)
+        sel = (rng.random(m) < 0.2) & (off != act)
+        mask[np.flatnonzero(sel), off[sel]] = 0
+    rew = rng.uniform(-1, 1, m).astype(np.float32)
+    val = rng.standard_normal(m).astype(np.float32)
+    logp = rng.standard_normal(m).astype(np.float32)
+    O = lo.OracleLearner(d, A, m + 1, hidden=H, with_baseline=True, train_vf_iters=1, seed=5)
+    pi0, v0 = [p.detach().clone() for p in O.pi], [p.detach().clone() for p in O.v]
+    from relayrl_b200 import Learner
+    L = Learner(d, A, m + 1, hidden=H, with_baseline=True, train_vf_iters=1)
+    L.set_params(0, lo.flatten(pi0).numpy())
+    L.set_params(1, lo.flatten(v0).numpy())
+    O.ingest(obs, act, mask, rew, val, logp, done)
+    L.ingest(obs, act, mask, rew, val, logp, done)
+    assert L.finish()[0] == n
+    data, _ = O.get()
+    ref = lo.train_epoch([p.double() for p in pi0], [p.double() for p in v0], {k: t.double() for k, t in data.items()},
+                         O.pi_lr, O.vf_lr, 1, return_grads=True)
+    ref32 = lo.train_epoch(pi0, v0, data, O.pi_lr, O.vf_lr, 1, return_grads=True)   # the reference's own arithmetic
+    for which, gkey, lkey in ((0, "pi_grad", "LossPi"), (1, "v_grad_first", "LossVOld")):
+        g, (loss, _, _) = L.eval_grad(which)
+        want, w32 = ref[gkey].numpy(), ref32[gkey].numpy().astype(np.float64)
+        # judged against float64: at least as close as twice the float32 reference's own distance, or 3e-6 of the
+        # largest entry (fp32 accumulation in windows of 1024 rows, float64 above), whichever is larger
+        e_gpu, e_ref = np.abs(g - want).max(), np.abs(w32 - want).max()
+        assert e_gpu <= max(2.0 * e_ref, 3e-6 * np.abs(want).max()), (gkey, e_gpu, e_ref, np.abs(want).max())
+        np.testing.assert_allclose(g, want, rtol=1e-5, atol=max(2.0 * e_ref, 3e-6 * np.abs(want).max()), err_msg=gkey)
+        np.testing.assert_allclose(loss, float(ref[lkey]), rtol=1e-5, atol=1e-7, err_msg=lkey)
+    L.close()
