@@ -205,6 +205,25 @@ def measure_scan(cols, offsets, last_vals, n, dev, with_baseline=True, reps=20):
     return sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
 
 
+# (21.161472 MB + 0.147968 MB) / 1 048 576 transitions, profiles/r1_tc_kernel_ncu_full_metrics.csv
+NCU_VALUE_KERNEL_BYTES_PER_TRANSITION = (21161472 + 147968) / 1048576.0
+# (538.012928 MB + 485.854208 MB) / 67 108 864 transitions, profiles/r1_scan_kernel_ncu_full_metrics.csv
+NCU_SCAN_KERNEL_BYTES_PER_TRANSITION = (538012928 + 485854208) / 67108864.0
+
+
+def linear_init(d, hidden, out, seed):
+    """torch.nn.Linear's default init (U(-1/sqrt(fan_in), 1/sqrt(fan_in))) for a d->hidden->hidden->out MLP, as a list
+    of (W [out,in], b) arrays in torch order and as the flat vector the C ABI takes.  bench.py's own copy: the
+    product side of the bench must not reach into oracle/."""
+    rng = np.random.default_rng(seed)
+    ps = []
+    for fan_in, fan_out in ((d, hidden), (hidden, hidden), (hidden, out)):
+        b = 1.0 / np.sqrt(fan_in)
+        ps.append(rng.uniform(-b, b, (fan_out, fan_in)).astype(np.float32))
+        ps.append(rng.uniform(-b, b, fan_out).astype(np.float32))
+    return ps, np.concatenate([p.reshape(-1) for p in ps])
+
+
 def measure_normalise(n, dev, reps=20):
     """K3 alone (the get()-style tap): 8 B per transition, median CUDA-event time on the launching stream."""
     import torch
@@ -228,11 +247,10 @@ def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=655
     the actor's own stream; beside it the oracle's step (torch CPU, all host threads) on the same shape."""
     import torch
     from relayrl_b200 import Actor
-    from oracle import learner_oracle as lo
-    pi, vf = lo.init_params(d, H_, A_, 11), lo.init_params(d, H_, 1, 12)
+    (pi_np, pi_flat), (vf_np, vf_flat) = linear_init(d, H_, A_, 11), linear_init(d, H_, 1, 12)
     act = Actor(d, A_, hidden=H_, with_baseline=True, device=dev.index or 0, max_batch=batch)
-    act.set_params(0, lo.flatten(pi).numpy())
-    act.set_params(1, lo.flatten(vf).numpy())
+    act.set_params(0, pi_flat)
+    act.set_params(1, vf_flat)
     g = torch.Generator(device="cpu").manual_seed(4)
     obs_h = torch.randn(batch, d, generator=g)
     mask_h = (torch.rand(batch, A_, generator=g) > 0.2).float()
@@ -251,6 +269,9 @@ def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=655
     torch.cuda.synchronize()
     ms = sorted(a.elapsed_time(b) for a, b in ev)[reps // 2]
     act.close()
+    # CPU baseline leg: the oracle's restatement of PolicyWithBaseline.step on the same weights
+    from oracle import learner_oracle as lo
+    pi, vf = [torch.from_numpy(p) for p in pi_np], [torch.from_numpy(p) for p in vf_np]
     torch.set_num_threads(os.cpu_count() or 1)
     lo.actor_step(pi, vf, obs_h[:cpu_batch], mask_h[:cpu_batch])
     t0 = time.perf_counter()
@@ -306,9 +327,8 @@ def run_ours(args):
     st = make_stream(n, 64 + rank, pinned=True)
     L = Learner(D, A, n + 1, hidden=H, with_baseline=True, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS,
                 device=local, rank=rank, nranks=world, nccl_id=nccl_id)
-    from oracle import learner_oracle as lo   # only for the (deterministic) initial weights
-    L.set_params(0, lo.flatten(lo.init_params(D, H, A, 1)).numpy())
-    L.set_params(1, lo.flatten(lo.init_params(D, H, 1, 2)).numpy())
+    L.set_params(0, linear_init(D, H, A, 1)[1])
+    L.set_params(1, linear_init(D, H, 1, 2)[1])
     cols, offsets, last_vals = device_columns(st, dev)
     torch.cuda.synchronize()
 
@@ -397,13 +417,19 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"kernel": "mlp_tc_kernel<VALUE> (fused value fwd+bwd: 3 GEMMs per 64-row tile on tcgen05, bf16x3)",
                      "bound": "tensor", "achieved": achieved_tf, "peak": bf16_sust, "unit": "TFLOP/s",
-                     "frac": achieved_tf / bf16_sust, "traffic": None, "peak_source": which + " bf16 sustained",
+                     "frac": achieved_tf / bf16_sust, "traffic": NCU_VALUE_KERNEL_BYTES_PER_TRANSITION * n,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture at 1 Mi "
+                                       "transitions (profiles/r1_tc_kernel_ncu_full_metrics.csv), scaled per transition; "
+                                       "algorithmic bytes are 20 per transition",
+                     "peak_source": which + " bf16 sustained",
                      "flops_per_launch": flops_per_launch, "launch_ms": value_launch_ms,
                      "executed_bf16_tflops": 6.0 * 3 * 2 * H * H * n / (value_launch_ms * 1e-3) / 1e12,
                      "note": "achieved = algorithmic fp32 flops (6*(D*H+H*H+H) per transition); each fp32 GEMM "
                              "is six bf16 MMAs (bf16x3 split), executed_bf16_tflops counts those"},
         "roofline_scan": {"kernel": "scan_kernel<with_baseline>", "bound": "hbm", "achieved": scan_gbs, "peak": hbm,
-                          "unit": "GB/s", "frac": scan_gbs / hbm, "traffic": None, "peak_source": which,
+                          "unit": "GB/s", "frac": scan_gbs / hbm, "traffic": NCU_SCAN_KERNEL_BYTES_PER_TRANSITION * n,
+                          "traffic_source": "ncu --set full at 64 Mi transitions (profiles/r1_scan_kernel_ncu_full_metrics.csv), "
+                                            "scaled per transition", "peak_source": which,
                           "bytes_per_transition": 16, "launch_ms": scan_ms},
         "stage_ms": {"scan": s["ms_scan"], "policy": s["ms_policy"], "value": s["ms_value"]},
         "cpu_baseline": {"value": cpu_tps, "unit": "transitions/s", "cores": cpu_threads, "kind": "port",
