@@ -39,7 +39,7 @@ constexpr int DZ_PLANE = tc::x_plane_bytes(TC_H, TILE_M), DZ_CHUNK = tc::x_chunk
 // TMEM columns: D1[2] (64 each; after epilogue 1 has read it, D1[k&1] is reused for planes 0 and 1 of H1^T, G3's A
 // operand), plane 2 of H1^T (32), D2 (64), dW2^T (128, one tile), ACC (128, the window's dW2^T sum)
 constexpr uint32_t TM_D1 = 0, TM_P2 = 128, TM_D2 = 160, TM_DW2 = 224, TM_ACC = 352, TM_COLS = 512;
-constexpr int NBUF = 3;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1 / prefetch)
+constexpr int NBUF = 4;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1), k+2 (in flight)
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
 // entries deep).  17 warps are allocated as 20, i.e. 96 registers per thread: the dW2 sums therefore live in
@@ -222,39 +222,49 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     auto inputs_landed = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
     // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units)
     auto stage1 = [&](int b) {
+        static_assert(TC_THREADS / 32 == TC_H / 8 && TILE_M == 64, "one warp per chunk of 8 hidden units, two rows per lane");
         const float *ob = obs_s + b * TILE_M * TC_MAX_D;
-#pragma unroll 1
-        for (int it = tid; it < TILE_M * (TC_H / 8); it += TC_THREADS) {
-            const int r = it & (TILE_M - 1), ch = it >> 6;  // a warp: 32 consecutive rows of one chunk
-            float4 x[TC_MAX_D / 4];
+        const int ch = warp;  // this warp's 8 hidden units; lane <-> rows lane and lane + 32 (W1 is loaded once for both)
+        float4 x[2][TC_MAX_D / 4];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr)
 #pragma unroll
             for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                x[i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&ob[r * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
-            const float4 ba = *reinterpret_cast<const float4 *>(&b1_s[8 * ch]), bb = *reinterpret_cast<const float4 *>(&b1_s[8 * ch + 4]);
-            const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-            uint32_t w1[4], w2[4], w3[4];
+                x[rr][i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&ob[(lane + 32 * rr) * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 ba = *reinterpret_cast<const float4 *>(&b1_s[8 * ch]), bb = *reinterpret_cast<const float4 *>(&b1_s[8 * ch + 4]);
+        const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        uint32_t p1[2][4], p2[2][4], p3[2][4];
 #pragma unroll
-            for (int e = 0; e < 8; e += 2) {
-                Trunc3 s[2];
+        for (int e = 0; e < 8; e += 2) {
+            Trunc3 s[2][2];
 #pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    const int u = 8 * ch + e + t;
-                    float acc = bias[e + t];
+            for (int t = 0; t < 2; ++t) {
+                const int u = 8 * ch + e + t;
+                float acc[2] = {bias[e + t], bias[e + t]};
 #pragma unroll
-                    for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                        if (4 * i4 < d) {  // W1 rows are zero padded
-                            const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
-                            acc = fmaf(x[i4].x, w.x, acc), acc = fmaf(x[i4].y, w.y, acc);
-                            acc = fmaf(x[i4].z, w.z, acc), acc = fmaf(x[i4].w, w.w, acc);
+                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
+                    if (4 * i4 < d) {  // W1 rows are zero padded
+                        const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
+#pragma unroll
+                        for (int rr = 0; rr < 2; ++rr) {
+                            acc[rr] = fmaf(x[rr][i4].x, w.x, acc[rr]), acc[rr] = fmaf(x[rr][i4].y, w.y, acc[rr]);
+                            acc[rr] = fmaf(x[rr][i4].z, w.z, acc[rr]), acc[rr] = fmaf(x[rr][i4].w, w.w, acc[rr]);
                         }
-                    s[t] = trunc3(fmaxf(acc, 0.f));
-                }
-                w1[e >> 1] = pack_hi16(s[0].t1, s[1].t1), w2[e >> 1] = pack_hi16(s[0].t2, s[1].t2), w3[e >> 1] = pack_hi16(s[0].t3, s[1].t3);
+                    }
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) s[rr][t] = trunc3(fmaxf(acc[rr], 0.f));
             }
-            const int o = ch * X_CHUNK + r * 16;
-            *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
-            *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(w2[0], w2[1], w2[2], w2[3]);
-            *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(w3[0], w3[1], w3[2], w3[3]);
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+                p1[rr][e >> 1] = pack_hi16(s[rr][0].t1, s[rr][1].t1), p2[rr][e >> 1] = pack_hi16(s[rr][0].t2, s[rr][1].t2),
+                p3[rr][e >> 1] = pack_hi16(s[rr][0].t3, s[rr][1].t3);
+        }
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+            const int o = ch * X_CHUNK + (lane + 32 * rr) * 16;
+            *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(p1[rr][0], p1[rr][1], p1[rr][2], p1[rr][3]);
+            *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(p2[rr][0], p2[rr][1], p2[rr][2], p2[rr][3]);
+            *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(p3[rr][0], p3[rr][1], p3[rr][2], p3[rr][3]);
         }
     };
     // the 16 worker warps meet at a named barrier; the MMA warp never joins it
@@ -408,7 +418,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     int k = 0;
     TCT_DECL;
     for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++k) {
-        const int b3 = k % NBUF, nb3 = (k + 1) % NBUF, pb3 = (k + 2) % NBUF;  // this, next, previous tile's inputs
+        const int b3 = k % NBUF, nb3 = (k + 1) % NBUF, pb3 = (k + NBUF - 1) % NBUF;  // this, next, previous tile's inputs
         const int64_t next = tile + gridDim.x, next2 = next + gridDim.x;
         const bool has_next = next < num_tiles;
         const float *rf = rowf_s + b3 * 3 * TILE_M;
@@ -419,10 +429,14 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         fence_after_sync();
 
         // ---- [A] stage 1 of the next tile; its G1 then runs under everything below --------------------------
+        // the inputs of tile k+2 start their way in (its buffer held tile k-2, dead since the previous iteration);
+        // those of tile k+1 landed before the barrier that ended the previous iteration
+        if (next2 < num_tiles) fetch_async(next2, (k + 2) % NBUF);
         if (has_next) {
-            inputs_landed();
-            fence_before_sync();
-            worker_sync();
+            if (k == 0) {  // tile 1 was fetched in the prologue
+                inputs_landed();
+                worker_sync();
+            }
             stage1(nb3);
             fence_smem_to_async();
             fence_before_sync();
@@ -457,9 +471,8 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
             fence_before_sync();
-            worker_sync();  // (also: every warp has read D1[k & 1] and has left the previous tile's input buffers)
+            worker_sync();  // (also: every warp has read D1[k & 1])
             fence_after_sync();
-            if (next2 < num_tiles) fetch_async(next2, pb3);
             // H1^T of this tile -> tensor memory (G3's A operand): recomputed from obs with thread = hidden unit, two rows
             // per 32-bit column; planes 0 and 1 go where D1[k & 1] was, plane 2 has its own 32 columns
             {
@@ -583,6 +596,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             }
             db2acc += dbl;
         }
+        inputs_landed();  // tile k+2's inputs (fetched a whole iteration ago) become visible with the barrier below
         fence_smem_to_async();
         fence_before_sync();
         worker_sync();
