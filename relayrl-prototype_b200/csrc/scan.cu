@@ -24,6 +24,8 @@
 //        memory and written with coalesced 128-bit stores
 //     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64.
 // Arithmetic is float64 with float32 storage, as in the reference.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace rrl {
@@ -120,6 +122,21 @@ __device__ __forceinline__ double f32_to_f64(float x)
     const unsigned hi = (u & 0x80000000u) | ((a >> 3) + 0x38000000u);
     return __hiloint2double(a ? hi : u, u << 29);
 }
+// The same without the branch: right for zero and normal numbers; f32_needs_slow() says when it is not.  The scan
+// tests all 8 (16) inputs of a thread at once and takes ONE branch to a slow copy of the loop, instead of one
+// convergence barrier (BSSY/BRA/BSYNC) per conversion -- those were 16 % of the instruction stream.
+__device__ __forceinline__ bool f32_needs_slow(float x)
+{
+    const unsigned a = __float_as_uint(x) & 0x7fffffffu;
+    return a - 0x00800000u >= 0x7f000000u && a != 0u;
+}
+__device__ __forceinline__ double f32_to_f64_fast(float x)
+{
+    const unsigned u = __float_as_uint(x);
+    const unsigned a = u & 0x7fffffffu;
+    const unsigned hi = (u & 0x80000000u) | ((a >> 3) + 0x38000000u);
+    return __hiloint2double(a ? hi : u, u << 29);
+}
 // d rounded to 24 significant bits, still a double (Veltkamp split with 2^29 + 1)
 __device__ __forceinline__ double round_to_f32_precision(double d)
 {
@@ -134,6 +151,19 @@ __device__ __forceinline__ float narrow_f32(double h, double d)
     const unsigned t = hi - 0x38000000u;             // exponent rebased from 1023 to 127 (sign untouched)
     if (((t << 1) >> 21) - 1u >= 254u) return f64_to_f32_slow(d);  // zero, f32-denormal range, overflow, Inf, NaN
     return __uint_as_float((hi & 0x80000000u) | __funnelshift_l(lo, t, 3));
+}
+// branch-free form + its validity test (same convention as above; an exact zero is handled in the fast form)
+__device__ __forceinline__ bool narrow_needs_slow(double h)
+{
+    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
+    const unsigned t = hi - 0x38000000u;
+    return ((t << 1) >> 21) - 1u >= 254u && ((hi << 1) | lo) != 0u;
+}
+__device__ __forceinline__ float narrow_f32_fast(double h)
+{
+    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
+    const unsigned bits = (hi & 0x80000000u) | __funnelshift_l(lo, hi - 0x38000000u, 3);
+    return __uint_as_float(((hi << 1) | lo) != 0u ? bits : (hi & 0x80000000u));
 }
 
 struct ScanArgs {
@@ -271,16 +301,23 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
 
     // ---- pass 1: this thread's map; inputs are widened once and kept (rr = reward, dl = the
     // GAE delta, both pure data) so that pass 2 is two DFMAs per transition ----------------------
+    // The widening is done branch-free; ONE test over all the thread's inputs sends a thread whose run holds a
+    // denormal, Inf or NaN to a copy of the loop that uses the exact (slow) conversion.
     Map m;
     double rr[SCAN_VPT], dl[WB ? SCAN_VPT : 1];
-    {
-        double ret_n = 0.0, adv_n = 0.0, v_n = WB ? f32_to_f64(v_edge) : 0.0;
+    bool in_slow = WB && f32_needs_slow(v_edge);
+#pragma unroll
+    for (int k = 0; k < SCAN_VPT; ++k) in_slow |= f32_needs_slow(r[k]) || (WB && f32_needs_slow(v[k]));
+    auto pass1 = [&](auto slow_tag) {
+        constexpr bool SLOW = decltype(slow_tag)::value;
+        auto widen = [](float x) { return SLOW ? f32_to_f64(x) : f32_to_f64_fast(x); };
+        double ret_n = 0.0, adv_n = 0.0, v_n = WB ? widen(v_edge) : 0.0;
         if (eb == 0u) {  // no path ends inside this thread's run (the common case)
 #pragma unroll
             for (int k = SCAN_VPT - 1; k >= 0; --k) {
-                rr[k] = f32_to_f64(r[k]);
+                rr[k] = widen(r[k]);
                 if (WB) {
-                    const double vk = f32_to_f64(v[k]);
+                    const double vk = widen(v[k]);
                     dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
                     v_n = vk;
                 }
@@ -302,9 +339,9 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                     ar = 0.0;
                     aa = 0.0;
                 }
-                rr[k] = f32_to_f64(r[k]);
+                rr[k] = widen(r[k]);
                 if (WB) {
-                    const double vk = f32_to_f64(v[k]);
+                    const double vk = widen(v[k]);
                     dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
                     v_n = vk;
                 }
@@ -316,7 +353,11 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
             m.ar = ar, m.aa = aa;
         }
         m.br = ret_n, m.ba = adv_n;
-    }
+    };
+    if (in_slow)
+        pass1(std::true_type{});
+    else
+        pass1(std::false_type{});
 
     // ---- warp suffix scan of the maps (lane l: M_l∘M_{l+1}∘...∘M_31) ----------------------------
     Map S = m;
@@ -398,28 +439,44 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
     consumer_sync();
 
     // ---- pass 2: final values, seeded with the carry ------------------------------------------
+    // Same scheme for the narrowing: branch-free, one test over the thread's 16 results; a thread with a result
+    // in the f32-denormal range, an overflow, Inf or NaN redoes its run with the exact (slow) conversion.
     double s1 = 0.0, s2 = 0.0;
     {
         const double wr = fma(Wsuf.ar, carry_s[0], Wsuf.br), wa = fma(Wsuf.aa, carry_s[1], Wsuf.ba);
-        double ret_n = fma(Ex.ar, wr, Ex.br), adv_n = fma(Ex.aa, wa, Ex.ba);
+        const double ret0 = fma(Ex.ar, wr, Ex.br), adv0 = fma(Ex.aa, wa, Ex.ba);
         float ao[SCAN_VPT], ro[SCAN_VPT];
+        auto pass2 = [&](auto slow_tag) -> bool {
+            constexpr bool SLOW = decltype(slow_tag)::value;
+            double ret_n = ret0, adv_n = adv0, t1 = 0.0, t2 = 0.0;
+            bool bad = false;
 #pragma unroll
-        for (int k = SCAN_VPT - 1; k >= 0; --k) {
-            if (eb != 0u && ((eb >> k) & 1u)) {
-                ret_n = WB ? f32_to_f64(B.lv[j0 + k]) : 0.0;
-                adv_n = 0.0;
+            for (int k = SCAN_VPT - 1; k >= 0; --k) {
+                if (eb != 0u && ((eb >> k) & 1u)) {
+                    ret_n = WB ? f32_to_f64(B.lv[j0 + k]) : 0.0;
+                    adv_n = 0.0;
+                }
+                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
+                ret_n = fma(a.gamma, ret_n, rr[k]);
+                const double ha = round_to_f32_precision(adv_n), hr = round_to_f32_precision(ret_n);
+                double x;  // the f32-rounded advantage, as the reference's buffer holds it
+                if (SLOW) {
+                    ao[k] = narrow_f32(ha, adv_n), ro[k] = narrow_f32(hr, ret_n);
+                    x = f32_to_f64(ao[k]);
+                } else {
+                    bad |= narrow_needs_slow(ha) || narrow_needs_slow(hr);
+                    ao[k] = narrow_f32_fast(ha), ro[k] = narrow_f32_fast(hr);
+                    x = ha;  // ha is exactly that f32 value, widened
+                }
+                if (j0 + k < cnt) {
+                    t1 += x;
+                    t2 = fma(x, x, t2);
+                }
             }
-            adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
-            ret_n = fma(a.gamma, ret_n, rr[k]);
-            const double ha = round_to_f32_precision(adv_n);
-            ao[k] = narrow_f32(ha, adv_n);
-            ro[k] = narrow_f32(round_to_f32_precision(ret_n), ret_n);
-            if (j0 + k < cnt) {
-                const double x = f32_to_f64(ao[k]);  // the f32-rounded advantage, as the reference's buffer holds it
-                s1 += x;
-                s2 = fma(x, x, s2);
-            }
-        }
+            s1 = t1, s2 = t2;
+            return bad;
+        };
+        if (pass2(std::false_type{})) pass2(std::true_type{});
         *reinterpret_cast<float4 *>(&r_s[sidx(j0)]) = make_float4(ao[0], ao[1], ao[2], ao[3]);
         *reinterpret_cast<float4 *>(&r_s[sidx(j0) + 4]) = make_float4(ao[4], ao[5], ao[6], ao[7]);
         *reinterpret_cast<float4 *>(&v_s[sidx(j0)]) = make_float4(ro[0], ro[1], ro[2], ro[3]);

@@ -209,3 +209,66 @@ def test_stateless_scan_device_large_properties():
     scan_device(d_rew * 4, d_val, d_offs, d_lvs, n, E, g, l, False, adv2, ret2, None, ws)
     torch.cuda.synchronize()
     assert torch.equal(adv2, adv * 4) and torch.equal(ret2, ret * 4)
+
+
+@pytest.mark.parametrize("wb", [True, False])
+def test_scan_special_values_take_the_slow_path(wb):
+    """Zeros, f32 denormals, results in the denormal range and results that overflow to Inf: the scan converts f32 <-> f64 with
+    branch-free integer arithmetic and sends a thread whose run holds such a value to the exact conversion;
+    both copies must agree with the C oracle (sequential f64 recurrence, IEEE narrowing)."""
+    import torch
+    from relayrl_b200 import scan_device, scan_workspace_bytes
+    rng = np.random.default_rng(11)
+    n = 40000
+    lens = []
+    while sum(lens) < n:
+        lens.append(int(rng.integers(1, 700)))
+    lens[-1] -= sum(lens) - n
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    E = len(lens)
+    rew = rng.uniform(-1, 1, n).astype(np.float32)
+    val = rng.standard_normal(n).astype(np.float32)
+    lvs = rng.uniform(-1, 1, E).astype(np.float32)
+    rew[1000:9000] = 0.0                                  # exact zeros in, exact zeros out (without baseline)
+    val[1000:9000] = 0.0
+    lvs[(offs[1:] > 1000) & (offs[1:] <= 9000)] = 0.0
+    rew[10000:10400] = np.float32(1e-41)                  # f32 denormal inputs
+    val[10200:10300] = np.float32(-3e-42)
+    rew[12000:16000] *= np.float32(1e-37)                 # results in the f32 denormal range
+    val[12000:16000] *= np.float32(1e-38)
+    rew[20000:20300] = np.float32(3e38)                   # discounted sums overflow to +Inf
+    dev = torch.device("cuda:0")
+    t = lambda a: torch.from_numpy(a).to(dev)
+    ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    g, l = float(np.float32(0.98)), float(np.float32(0.97))
+
+    def run(rew_, val_):
+        adv, ret = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        scan_device(t(rew_), t(val_), t(offs), t(lvs), n, E, g, l, wb, adv, ret, None, ws)
+        torch.cuda.synchronize()
+        return adv.cpu().numpy(), ret.cpu().numpy()
+
+    got_a, got_r = run(rew, val)
+    with np.errstate(all="ignore"):
+        a_ref, r_ref = sr.finish_paths(rew, val, offs, lvs, g, l, wb)
+    for got, ref, name in ((got_a, a_ref, "adv"), (got_r, r_ref, "ret")):
+        assert not np.isnan(got).any() and not np.isnan(ref).any(), name
+        assert np.array_equal(np.isinf(got), np.isinf(ref)), name
+        fin = np.isfinite(ref)
+        assert np.array_equal(np.sign(got[~fin]), np.sign(ref[~fin])), name
+        # denormal results: absolute agreement to one f32 denormal step; elsewhere the usual 1e-6
+        np.testing.assert_allclose(got[fin], ref[fin], rtol=RTOL, atol=2e-45, err_msg=name)
+        assert np.mean(got[fin] != ref[fin]) < 1e-3, name
+    assert np.isinf(got_r).any()
+    if not wb:
+        assert (got_r[1000:9000] == 0).any() and (np.abs(got_r[12000:16000]) < 1.2e-38).any()
+    # Non-finite INPUTS are outside the parity contract (in the reference one NaN reward turns the advantage
+    # statistics, and with them every weight, into NaN; here 0 * NaN additionally crosses the episode boundary to
+    # the left because a path end is a zero slope of the affine map).  What must hold: the call completes (a data
+    # NaN is never mistaken for the look-back's "unset" sentinel) and the poisoned element itself is NaN.
+    rew2, val2 = rew.copy(), val.copy()
+    rew2[25000] = np.float32("nan")
+    val2[30000] = np.float32("inf")
+    got_a, got_r = run(rew2, val2)
+    assert np.isnan(got_r[25000]) and np.isnan(got_a[25000])
+    assert np.isfinite(got_r[39000:]).all()
