@@ -207,8 +207,8 @@ def measure_scan(cols, offsets, last_vals, n, dev, with_baseline=True, reps=20):
 
 # (21.161472 MB + 0.147968 MB) / 1 048 576 transitions, profiles/r1_tc_kernel_ncu_full_metrics.csv
 NCU_VALUE_KERNEL_BYTES_PER_TRANSITION = (21161472 + 147968) / 1048576.0
-# (538.012928 MB + 485.854208 MB) / 67 108 864 transitions, profiles/r1_scan_kernel_ncu_full_metrics.csv
-NCU_SCAN_KERNEL_BYTES_PER_TRANSITION = (538012928 + 485854208) / 67108864.0
+# (537.989120 MB + 485.492736 MB) / 67 108 864 transitions, profiles/r1_scan_kernel_ncu_full_metrics.csv
+NCU_SCAN_KERNEL_BYTES_PER_TRANSITION = (537989120 + 485492736) / 67108864.0
 
 
 def linear_init(d, hidden, out, seed):
