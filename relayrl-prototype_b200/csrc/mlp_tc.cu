@@ -17,7 +17,7 @@
 // comes from the order of work): G3 goes first; as soon as it retires the H1 planes are free and stage 1 of
 // the NEXT tile runs under G2; G1 of the next tile is issued before epilogue 2 of this one and runs under it.
 // The tile inputs are fetched from global memory one tile ahead.  dW2 is drained from TMEM into per-thread
-// f32 sums after every tile; every FLUSH_TILES tiles everything spills into the CTA's float64 partials
+// f32 sums after every tile; every TC_FLUSH (32) tiles everything spills into the CTA's float64 partials
 // exactly like the CUDA-core kernel.
 #include "mlp_internal.cuh"
 #include "tc_common.cuh"
@@ -39,6 +39,9 @@ constexpr int DZ_PLANE = tc::x_plane_bytes(TC_H, TILE_M), DZ_CHUNK = tc::x_chunk
 // TMEM columns: D1[2] (64 each; after epilogue 1 has read it, D1[k&1] is reused for planes 0 and 1 of H1^T, G3's A
 // operand), plane 2 of H1^T (32), D2 (64), dW2^T (128, one tile), ACC (128, the window's dW2^T sum)
 constexpr uint32_t TM_D1 = 0, TM_P2 = 128, TM_D2 = 160, TM_DW2 = 224, TM_ACC = 352, TM_COLS = 512;
+// f32 accumulation window of this kernel: 32 tiles = 2048 transitions, then the float64 spill (the CUDA-core kernel
+// uses 16; here a spill costs two barriers and 32 reductions per thread: 5.5 % of a tile at 16, 2.7 % at 32)
+constexpr int TC_FLUSH = 2 * FLUSH_TILES;
 constexpr int NBUF = 4;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1), k+2 (in flight)
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
@@ -329,9 +332,10 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         db1acc += dbl;
     };
     // ---- drain tile kk's dW2^T (TMEM lane = in unit j, this warp's 32 out units) into the window sum in TMEM ----
-    auto drain = [&](int kk, bool first_in_window) {
-        mbar_wait(bar3, (uint32_t)(kk & 1));
+    auto drain = [&](int kk) {
+        mbar_wait(bar3, (uint32_t)(kk & 1));  // (also: G3(kk) no longer reads the dZ2 planes)
         fence_after_sync();
+        const bool first_in_window = kk % TC_FLUSH == 0;
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
             float v[16], s[16];
@@ -447,11 +451,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 
         // ---- [D] the previous tile's tail: its G3 and G2 retired long ago -----------------------------------------
         if (k > 0) {
-            drain(k - 1, (k - 1) % FLUSH_TILES == 0);
+            drain(k - 1);
             TCT(7);
             epilogue2(k - 1, pb3);
             TCT(10);
-            if (k % FLUSH_TILES == 0) spill();
+            if (k % TC_FLUSH == 0) spill();
             TCT(11);
         }
 
@@ -605,7 +609,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     }
     // ---- pipeline tail: the last tile's drain, epilogue 2 and the final spill ------------------------------------
     if (k > 0) {
-        drain(k - 1, (k - 1) % FLUSH_TILES == 0);
+        drain(k - 1);
         epilogue2(k - 1, (k - 1) % NBUF);
         spill();
     }
