@@ -284,6 +284,44 @@ def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=655
             "cpu_env_steps_per_s": cpu_batch / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
 
 
+def measure_without_baseline(dev, local, n=1 << 20, reps=5):
+    """C2: REINFORCE without baseline on a 1 Mi-transition batch: ingest from pinned host memory,
+    scan, statistics, one policy step; CUDA events on the learner's stream.  Beside it the oracle port on the host."""
+    import torch
+    from relayrl_b200 import Learner, _lib
+    from relayrl_b200._lib import BatchView
+    st = make_stream(n, 1234, pinned=True)
+    L = Learner(D, A, n + 1, hidden=H, with_baseline=False, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS, device=local)
+    L.set_params(0, linear_init(D, H, A, 1)[1])
+    view = BatchView(st["obs"].data_ptr(), st["act"].data_ptr(), st["mask"].data_ptr(), st["rew"].data_ptr(),
+                     st["val"].data_ptr(), st["logp"].data_ptr(), st["done"].data_ptr(), st["rows"], _lib.RRL_F32,
+                     _lib.RRL_F32)
+    ls = torch.cuda.ExternalStream(L.stream, device=dev)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+    for i in range(2 + reps):
+        if i >= 2:
+            ev[i - 2][0].record(ls)
+        L.ingest_raw(view)
+        stats = L.train_epoch()
+        if i >= 2:
+            ev[i - 2][1].record(ls)
+    torch.cuda.synchronize()
+    ms = sorted(a.elapsed_time(b) for a, b in ev)[reps // 2]
+    L.close()
+    # CPU leg: the oracle port, same stream, all host threads
+    from oracle import learner_oracle as lo
+    torch.set_num_threads(os.cpu_count() or 1)
+    O = lo.OracleLearner(D, A, n + 1, hidden=H, with_baseline=False, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS, seed=1)
+    t0 = time.perf_counter()
+    O.ingest(st["obs"].numpy(), st["act"].numpy(), st["mask"].numpy(), st["rew"].numpy(), st["val"].numpy(),
+             st["logp"].numpy(), st["done"].numpy())
+    O.train()
+    cpu_s = time.perf_counter() - t0
+    return {"workload": "C2: REINFORCE without baseline, %d transitions, host ingest + scan + statistics + 1 policy step" % n,
+            "transitions_per_s": n / (ms * 1e-3), "ms_per_epoch": ms, "stage_ms": {"scan": stats["ms_scan"], "policy": stats["ms_policy"]},
+            "cpu_transitions_per_s": n / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
+
+
 def run_scan_only(args):
     import torch
     dev = torch.device("cuda", 0)
@@ -390,6 +428,7 @@ def run_ours(args):
                                         "achieved": 8.0 * n / (norm_ms * 1e-3) / 1e9, "unit": "GB/s", "launch_ms": norm_ms,
                                         "bytes_per_transition": 8}
         extras["actor"] = measure_actor(dev)
+        extras["without_baseline"] = measure_without_baseline(dev, local)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
