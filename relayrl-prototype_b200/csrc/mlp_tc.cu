@@ -103,7 +103,9 @@ __device__ unsigned long long g_tc_timing[16];
 #define TCT(slot)
 #endif
 
-template <int MODE>
+// D4 = ceil(obs_dim / 4) as a compile-time constant: with a run-time bound the obs_dim = 4 case issued every FFMA and
+// LDS of the unused upper half predicated off -- half of all FFMA issue slots
+template <int MODE, int D4>
 __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -181,11 +183,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     // its fp32 accumulator with truncation (measured bias -4e-8 per MMA), so letting dW2 ride in TMEM
     // across tiles cost ~4e-6 of accuracy after 8 tiles; 24 MMAs per drain keep it at the CUDA-core level.
     // (the sums themselves sit in TMEM columns TM_ACC.., same lane/column ownership as the drain)
-    float dW3acc[TC_MAX_OUT], dW1acc[TC_MAX_D], db1acc = 0.f, db2acc = 0.f, db3acc[TC_MAX_OUT];
+    float dW3acc[TC_MAX_OUT], dW1acc[4 * D4], db1acc = 0.f, db2acc = 0.f, db3acc[TC_MAX_OUT];
 #pragma unroll
     for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
+    for (int i = 0; i < 4 * D4; ++i) dW1acc[i] = 0.f;
     double l0 = 0.0, l1 = 0.0, l2 = 0.0;
     bool first_flush = true;
     double *my_partials = a.partials + (size_t)blockIdx.x * a.n_params;
@@ -228,12 +230,12 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         static_assert(TC_THREADS / 32 == TC_H / 8 && TILE_M == 64, "one warp per chunk of 8 hidden units, two rows per lane");
         const float *ob = obs_s + b * TILE_M * TC_MAX_D;
         const int ch = warp;  // this warp's 8 hidden units; lane <-> rows lane and lane + 32 (W1 is loaded once for both)
-        float4 x[2][TC_MAX_D / 4];
+        float4 x[2][D4];
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr)
 #pragma unroll
-            for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                x[rr][i4] = (4 * i4 < d) ? *reinterpret_cast<const float4 *>(&ob[(lane + 32 * rr) * TC_MAX_D + 4 * i4]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i4 = 0; i4 < D4; ++i4)
+                x[rr][i4] = *reinterpret_cast<const float4 *>(&ob[(lane + 32 * rr) * TC_MAX_D + 4 * i4]);
         const float4 ba = *reinterpret_cast<const float4 *>(&b1_s[8 * ch]), bb = *reinterpret_cast<const float4 *>(&b1_s[8 * ch + 4]);
         const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
         uint32_t p1[2][4], p2[2][4], p3[2][4];
@@ -245,8 +247,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 const int u = 8 * ch + e + t;
                 float acc[2] = {bias[e + t], bias[e + t]};
 #pragma unroll
-                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                    if (4 * i4 < d) {  // W1 rows are zero padded
+                for (int i4 = 0; i4 < D4; ++i4) {  // W1 rows are zero padded
                         const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
 #pragma unroll
                         for (int rr = 0; rr < 2; ++rr) {
@@ -319,8 +320,8 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             const float dz1 = ((hb >> c) & 1u) ? dh[c] : 0.f;
             dbl += dz1;
 #pragma unroll
-            for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) {
-                if (4 * i4 < d) {
+            for (int i4 = 0; i4 < D4; ++i4) {
+                {
                     const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
                     dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
                     dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
@@ -374,7 +375,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
         for (int i = 0; i < TC_MAX_OUT; ++i) mine[2 + i] = dW3acc[i];
 #pragma unroll
-        for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = dW1acc[i];
+        for (int i = 0; i < TC_MAX_D; ++i) mine[2 + TC_MAX_OUT + i] = i < 4 * D4 ? dW1acc[i] : 0.f;
         float *stage3 = stage + TC_RG * TC_H * S;  // [64][MAX_OUT] per-row dhead sums
         if (q == 0 && lane < TC_RPT)
 #pragma unroll
@@ -401,7 +402,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
         for (int i = 0; i < TC_MAX_OUT; ++i) dW3acc[i] = 0.f, db3acc[i] = 0.f;
 #pragma unroll
-        for (int i = 0; i < TC_MAX_D; ++i) dW1acc[i] = 0.f;
+        for (int i = 0; i < 4 * D4; ++i) dW1acc[i] = 0.f;
         first_flush = false;
         worker_sync();  // the staging area is read: epilogue 1 may write the dZ2 planes again
     };
@@ -481,9 +482,9 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             // per 32-bit column; planes 0 and 1 go where D1[k & 1] was, plane 2 has its own 32 columns
             {
                 const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
-                float4 w1r[TC_MAX_D / 4];
+                float4 w1r[D4];
 #pragma unroll
-                for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
+                for (int i4 = 0; i4 < D4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
                 const float b1 = b1_s[j];
                 uint32_t hk[3][TC_RPT / 2], hbits = 0u;
 #pragma unroll
@@ -494,8 +495,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                         const int m = TC_RPT * rq + c + t;
                         float acc = b1;
 #pragma unroll
-                        for (int i4 = 0; i4 < TC_MAX_D / 4; ++i4)
-                            if (4 * i4 < d) {  // same operation order as stage 1: the two copies of H1 are identical
+                        for (int i4 = 0; i4 < D4; ++i4) {  // same operation order as stage 1: the two copies of H1 are identical
                                 const float4 x = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
                                 acc = fmaf(x.x, w1r[i4].x, acc), acc = fmaf(x.y, w1r[i4].y, acc);
                                 acc = fmaf(x.z, w1r[i4].z, acc), acc = fmaf(x.w, w1r[i4].w, acc);
@@ -656,18 +656,20 @@ bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad)
 
 size_t tc_smem_bytes() { return TC_SMEM_BYTES; }
 
-int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, cudaStream_t stream, ErrBuf &err)
+template <int MODE, int D4>
+static int32_t tc_launch_one(const MlpArgs &a, int grid, cudaStream_t stream, ErrBuf &err)
 {
-    (void)nd;
-    if (mode == MODE_VALUE) {
-        RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_VALUE>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_VALUE><<<grid, TC_CTA_THREADS, TC_SMEM_BYTES, stream>>>(a);
-    } else {
-        RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE_POLICY_REF>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
-        mlp_tc_kernel<MODE_POLICY_REF><<<grid, TC_CTA_THREADS, TC_SMEM_BYTES, stream>>>(a);
-    }
+    RRL_CUDA_OK(cudaFuncSetAttribute(mlp_tc_kernel<MODE, D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES), err);
+    mlp_tc_kernel<MODE, D4><<<grid, TC_CTA_THREADS, TC_SMEM_BYTES, stream>>>(a);
     RRL_CUDA_OK(cudaGetLastError(), err);
     return RRL_OK;
+}
+
+int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, cudaStream_t stream, ErrBuf &err)
+{
+    const bool wide = nd.d > 4;
+    if (mode == MODE_VALUE) return wide ? tc_launch_one<MODE_VALUE, 2>(a, grid, stream, err) : tc_launch_one<MODE_VALUE, 1>(a, grid, stream, err);
+    return wide ? tc_launch_one<MODE_POLICY_REF, 2>(a, grid, stream, err) : tc_launch_one<MODE_POLICY_REF, 1>(a, grid, stream, err);
 }
 
 }  // namespace rrl
