@@ -8,6 +8,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "learner.cuh"
@@ -225,107 +227,147 @@ struct HostColumns {
     int64_t cap;
 };
 
-// Decodes one serialized Trajectory into SoA rows (terminal markers become rows with done = 1 that carry
-// only their reward, as rrl_batch_view_t expects).
-static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int A, bool with_baseline, const HostColumns &o,
-                                      int64_t &count, ErrBuf &err)
+// One action sub-message -> row r of the columns.  Returns RRL_OK or RRL_EFORMAT with `err` set.
+static int32_t decode_grpc_action(Cur act, int64_t r, int d, int A, bool with_baseline, const HostColumns &o,
+                                  std::vector<uint8_t> &scratch, ErrBuf &err)
 {
-    count = 0;
-    std::vector<uint8_t> scratch;
-    Cur top{msg, msg + len};
-    while (top.p < top.end) {
-        uint64_t key;
-        if (!rd_varint(top, key)) goto truncated;
-        if (key != ((1u << 3) | 2u)) {
-            if (!skip_field(top, (unsigned)(key & 7))) goto truncated;
-            continue;
-        }
-        Cur act;
-        if (!rd_len(top, act)) goto truncated;
-        if (count >= o.cap) {
-            err.set("trajectory holds more than the %lld rows the caller provided", (long long)o.cap);
-            return RRL_ECAPACITY;
-        }
+    Cur f_obs{nullptr, nullptr}, f_act{nullptr, nullptr}, f_mask{nullptr, nullptr}, f_logp{nullptr, nullptr}, f_v{nullptr, nullptr};
+    float rew = 0.f;
+    bool done = false;
+    while (act.p < act.end) {
+        uint64_t k;
+        if (!rd_varint(act, k)) goto truncated;
         {
-            Cur f_obs{nullptr, nullptr}, f_act{nullptr, nullptr}, f_mask{nullptr, nullptr}, f_logp{nullptr, nullptr}, f_v{nullptr, nullptr};
-            float rew = 0.f;
-            bool done = false;
-            while (act.p < act.end) {
-                uint64_t k;
-                if (!rd_varint(act, k)) goto truncated;
-                const unsigned field = (unsigned)(k >> 3), wt = (unsigned)(k & 7);
-                if (field >= 1 && field <= 3 && wt == 2) {
-                    Cur b;
-                    if (!rd_len(act, b)) goto truncated;
-                    (field == 1 ? f_obs : field == 2 ? f_act : f_mask) = b;
-                } else if (field == 4 && wt == 5) {
-                    if (act.end - act.p < 4) goto truncated;
-                    memcpy(&rew, act.p, 4);
-                    act.p += 4;
-                } else if (field == 5 && wt == 2) {  // one map entry: { string key = 1; bytes value = 2; }
-                    Cur e, kstr{nullptr, nullptr}, val{nullptr, nullptr};
-                    if (!rd_len(act, e)) goto truncated;
-                    while (e.p < e.end) {
-                        uint64_t ek;
-                        if (!rd_varint(e, ek)) goto truncated;
-                        if ((ek & 7) == 2 && (ek >> 3) == 1) {
-                            if (!rd_len(e, kstr)) goto truncated;
-                        } else if ((ek & 7) == 2 && (ek >> 3) == 2) {
-                            if (!rd_len(e, val)) goto truncated;
-                        } else if (!skip_field(e, (unsigned)(ek & 7))) {
-                            goto truncated;
-                        }
+            const unsigned field = (unsigned)(k >> 3), wt = (unsigned)(k & 7);
+            if (field >= 1 && field <= 3 && wt == 2) {
+                Cur b;
+                if (!rd_len(act, b)) goto truncated;
+                (field == 1 ? f_obs : field == 2 ? f_act : f_mask) = b;
+            } else if (field == 4 && wt == 5) {
+                if (act.end - act.p < 4) goto truncated;
+                memcpy(&rew, act.p, 4);
+                act.p += 4;
+            } else if (field == 5 && wt == 2) {  // one map entry: { string key = 1; bytes value = 2; }
+                Cur e, kstr{nullptr, nullptr}, val{nullptr, nullptr};
+                if (!rd_len(act, e)) goto truncated;
+                while (e.p < e.end) {
+                    uint64_t ek;
+                    if (!rd_varint(e, ek)) goto truncated;
+                    if ((ek & 7) == 2 && (ek >> 3) == 1) {
+                        if (!rd_len(e, kstr)) goto truncated;
+                    } else if ((ek & 7) == 2 && (ek >> 3) == 2) {
+                        if (!rd_len(e, val)) goto truncated;
+                    } else if (!skip_field(e, (unsigned)(ek & 7))) {
+                        goto truncated;
                     }
-                    const size_t kl = (size_t)(kstr.end - kstr.p);
-                    if (kl == 6 && !memcmp(kstr.p, "logp_a", 6)) f_logp = val;
-                    else if (kl == 1 && kstr.p[0] == 'v') f_v = val;
-                } else if (field == 6 && wt == 0) {
-                    uint64_t b;
-                    if (!rd_varint(act, b)) goto truncated;
-                    done = b != 0;
-                } else if (!skip_field(act, wt)) {
-                    goto truncated;
                 }
+                const size_t kl = (size_t)(kstr.end - kstr.p);
+                if (kl == 6 && !memcmp(kstr.p, "logp_a", 6)) f_logp = val;
+                else if (kl == 1 && kstr.p[0] == 'v') f_v = val;
+            } else if (field == 6 && wt == 0) {
+                uint64_t b;
+                if (!rd_varint(act, b)) goto truncated;
+                done = b != 0;
+            } else if (!skip_field(act, wt)) {
+                goto truncated;
             }
-            const int64_t r = count;
-            o.rew[r] = rew, o.done[r] = done ? 1 : 0;
-            o.act[r] = 0.f, o.val[r] = 0.f, o.logp[r] = 0.f;
-            for (int i = 0; i < d; ++i) o.obs[r * d + i] = 0.f;
-            for (int i = 0; i < A; ++i) o.mask[r * A + i] = 0.f;
-            if (!done) {  // a terminal marker has obs = act = mask = data = None (agent_zmq.rs:607-608)
-                BlobView bo, ba, bm;
-                RRL_TRY(parse_blob(f_obs.p, (size_t)(f_obs.end - f_obs.p), bo, err));
-                RRL_TRY(parse_blob(f_act.p, (size_t)(f_act.end - f_act.p), ba, err));
-                RRL_TRY(parse_blob(f_mask.p, (size_t)(f_mask.end - f_mask.p), bm, err));
-                if ((int)bo.count != d || (int)bm.count != A || ba.count < 1) {
-                    err.set("action %lld: obs has %zu values (want %d), mask %zu (want %d), act %zu", (long long)r, bo.count, d,
-                            bm.count, A, ba.count);
-                    return RRL_EFORMAT;
-                }
-                for (int i = 0; i < d; ++i) o.obs[r * d + i] = blob_at(bo, i);
-                for (int i = 0; i < A; ++i) o.mask[r * A + i] = blob_at(bm, i);
-                o.act[r] = blob_at(ba, 0);
-                if (!f_logp.p) {
-                    err.set("action %lld: data['logp_a'] missing", (long long)r);
-                    return RRL_EFORMAT;
-                }
-                RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_logp.p), (size_t)(f_logp.end - f_logp.p), scratch, o.logp[r],
-                                         "logp_a", err));
-                if (with_baseline) {
-                    if (!f_v.p) {
-                        err.set("action %lld: data['v'] missing", (long long)r);
-                        return RRL_EFORMAT;
-                    }
-                    RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_v.p), (size_t)(f_v.end - f_v.p), scratch, o.val[r], "v", err));
-                }
+        }
+    }
+    o.rew[r] = rew, o.done[r] = done ? 1 : 0;
+    o.act[r] = 0.f, o.val[r] = 0.f, o.logp[r] = 0.f;
+    for (int i = 0; i < d; ++i) o.obs[r * d + i] = 0.f;
+    for (int i = 0; i < A; ++i) o.mask[r * A + i] = 0.f;
+    if (!done) {  // a terminal marker has obs = act = mask = data = None (agent_zmq.rs:607-608)
+        BlobView bo, ba, bm;
+        RRL_TRY(parse_blob(f_obs.p, (size_t)(f_obs.end - f_obs.p), bo, err));
+        RRL_TRY(parse_blob(f_act.p, (size_t)(f_act.end - f_act.p), ba, err));
+        RRL_TRY(parse_blob(f_mask.p, (size_t)(f_mask.end - f_mask.p), bm, err));
+        if ((int)bo.count != d || (int)bm.count != A || ba.count < 1) {
+            err.set("action %lld: obs has %zu values (want %d), mask %zu (want %d), act %zu", (long long)r, bo.count, d, bm.count,
+                    A, ba.count);
+            return RRL_EFORMAT;
+        }
+        for (int i = 0; i < d; ++i) o.obs[r * d + i] = blob_at(bo, i);
+        for (int i = 0; i < A; ++i) o.mask[r * A + i] = blob_at(bm, i);
+        o.act[r] = blob_at(ba, 0);
+        if (!f_logp.p) {
+            err.set("action %lld: data['logp_a'] missing", (long long)r);
+            return RRL_EFORMAT;
+        }
+        RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_logp.p), (size_t)(f_logp.end - f_logp.p), scratch, o.logp[r],
+                                 "logp_a", err));
+        if (with_baseline) {
+            if (!f_v.p) {
+                err.set("action %lld: data['v'] missing", (long long)r);
+                return RRL_EFORMAT;
             }
-            ++count;
+            RRL_TRY(parse_data_value(reinterpret_cast<const char *>(f_v.p), (size_t)(f_v.end - f_v.p), scratch, o.val[r], "v", err));
         }
     }
     return RRL_OK;
 truncated:
-    err.set("serialized Trajectory is truncated or not proto3 wire format (at byte %zu of %zu)", (size_t)(top.p - msg), len);
+    err.set("action %lld of the serialized Trajectory is truncated or not proto3 wire format", (long long)r);
     return RRL_EFORMAT;
+}
+
+// Decodes one serialized Trajectory into SoA rows (terminal markers become rows with done = 1 that carry only
+// their reward, as rrl_batch_view_t expects).  Two passes: the top-level fields are walked once to index the
+// action sub-messages (cheap: one varint pair each), then the actions -- ~420 B of safetensors blobs and ~500 B of
+// JSON byte arrays apiece, the expensive part -- are decoded independently, on several host threads when the
+// message is large.  On failure the error of the lowest-numbered bad action is reported, as a serial decoder would.
+static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int A, bool with_baseline, const HostColumns &o,
+                                      int64_t &count, ErrBuf &err)
+{
+    count = 0;
+    std::vector<Cur> actions;
+    Cur top{msg, msg + len};
+    while (top.p < top.end) {
+        uint64_t key;
+        Cur sub;
+        const bool ok = rd_varint(top, key) && (key == ((1u << 3) | 2u) ? rd_len(top, sub) : skip_field(top, (unsigned)(key & 7)));
+        if (!ok) {
+            err.set("serialized Trajectory is truncated or not proto3 wire format (at byte %zu of %zu)", (size_t)(top.p - msg), len);
+            return RRL_EFORMAT;
+        }
+        if (key == ((1u << 3) | 2u)) actions.push_back(sub);
+    }
+    const int64_t n = (int64_t)actions.size();
+    if (n > o.cap) {
+        err.set("trajectory holds %lld actions, more than the %lld rows the caller provided", (long long)n, (long long)o.cap);
+        return RRL_ECAPACITY;
+    }
+    unsigned hw = std::thread::hardware_concurrency();
+    const int64_t per_thread_min = 2048;  // below this a thread costs more than it saves
+    const int nthreads = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)(hw ? hw : 1), 16, n / per_thread_min}));
+    std::vector<int32_t> status(nthreads, RRL_OK);
+    std::vector<ErrBuf> errs(nthreads);
+    auto work = [&](int t) {
+        std::vector<uint8_t> scratch;
+        scratch.reserve(256);
+        const int64_t lo = n * t / nthreads, hi = n * (t + 1) / nthreads;
+        for (int64_t r = lo; r < hi; ++r) {
+            const int32_t st = decode_grpc_action(actions[(size_t)r], r, d, A, with_baseline, o, scratch, errs[t]);
+            if (st != RRL_OK) {
+                status[t] = st;
+                return;  // later actions of this range are not needed: the call fails
+            }
+        }
+    };
+    if (nthreads == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
+        work(0);
+        for (auto &th : pool) th.join();
+    }
+    for (int t = 0; t < nthreads; ++t)  // ranges are in action order: the first failing range holds the first bad action
+        if (status[t] != RRL_OK) {
+            err.msg = errs[t].msg;
+            return status[t];
+        }
+    count = n;
+    return RRL_OK;
 }
 
 }  // namespace rrl

@@ -117,3 +117,25 @@ def test_malformed_inputs_fail_loudly():
     with pytest.raises(RelayRLB200Error) as e:
         decode_grpc_trajectory(msg, 4, 2, True, cap=2)
     assert e.value.status == -3
+
+
+def test_large_message_decodes_on_several_threads():
+    """Above 2048 actions per thread the decoder splits the action list over host threads; the result and the
+    error reporting (lowest-numbered bad action) must not depend on that."""
+    msg1, want1 = _trajectory(np.random.default_rng(9), 1500, 4, 2)
+    reps = 6                                     # 9006 actions: four threads
+    msg = msg1 * reps                            # concatenated serialisations of a repeated field = one message with all
+    got = decode_grpc_trajectory(msg, 4, 2, True)
+    assert len(got["rew"]) == reps * 1501
+    for k in want1:
+        assert np.array_equal(got[k], np.concatenate([want1[k].astype(got[k].dtype)] * reps)), k
+    # two bad actions (obs of the wrong width) in different threads' ranges: the first one is reported
+    Action, Trajectory = _messages()
+    bad = Trajectory()
+    a = bad.actions.add(obs=_blob(np.zeros(7)), action=_blob(np.zeros(1, np.float32)), mask=_blob(np.ones(2)), reward=1.0)
+    a.data["logp_a"] = _tensor_json(np.zeros(1, np.float32), "Float")
+    a.data["v"] = _tensor_json(np.zeros((), np.float32), "Float")
+    bad = bad.SerializeToString()
+    msg = msg1 * 2 + bad + msg1 * 3 + bad + msg1
+    with pytest.raises(RelayRLB200Error, match="action 3002: obs has 7 values"):
+        decode_grpc_trajectory(msg, 4, 2, True)
