@@ -28,7 +28,7 @@ static int32_t dmalloc(T **p, size_t count, ErrBuf &err, bool zero = true)
     return RRL_OK;
 }
 
-int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, ErrBuf &err)
+int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bool data_parallel, ErrBuf &err)
 {
     net.dims = NetDims{d, H, out};
     net.step = 0;
@@ -36,6 +36,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, Er
     const size_t P = (size_t)net.dims.n_params();
     RRL_TRY(dmalloc(&net.params, P, err));
     net.grad = net.m = net.v = nullptr;
+    net.grad64 = nullptr;
     net.partials64 = net.loss_partials = net.loss_out = nullptr;
     if (train) {
         RRL_TRY(dmalloc(&net.grad, P, err));
@@ -44,6 +45,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, Er
         RRL_TRY(dmalloc(&net.partials64, P * (size_t)grid, err));
         RRL_TRY(dmalloc(&net.loss_partials, 4 * (size_t)grid, err));
         RRL_TRY(dmalloc(&net.loss_out, 4, err));
+        if (data_parallel) RRL_TRY(dmalloc(&net.grad64, P, err));
     }
     return RRL_OK;
 }
@@ -51,7 +53,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, Er
 void net_free(NetState &net)
 {
     cudaFree(net.params), cudaFree(net.grad), cudaFree(net.m), cudaFree(net.v);
-    cudaFree(net.partials64), cudaFree(net.loss_partials), cudaFree(net.loss_out);
+    cudaFree(net.partials64), cudaFree(net.loss_partials), cudaFree(net.loss_out), cudaFree(net.grad64);
     net = NetState{};
 }
 
@@ -395,8 +397,8 @@ int32_t rrl_learner_create(const rrl_config_t *cfg, rrl_learner_t **out)
         s.bytes = sm.total;
     }
     const int grid = mlp_grid_for_device(cfg->device, cfg->hidden);
-    C_TRY(net_alloc(h->pi, cfg->obs_dim, cfg->hidden, cfg->act_dim, grid, true, h->err));
-    if (cfg->with_baseline) C_TRY(net_alloc(h->vf, cfg->obs_dim, cfg->hidden, 1, grid, true, h->err));
+    C_TRY(net_alloc(h->pi, cfg->obs_dim, cfg->hidden, cfg->act_dim, grid, true, cfg->nranks > 1, h->err));
+    if (cfg->with_baseline) C_TRY(net_alloc(h->vf, cfg->obs_dim, cfg->hidden, 1, grid, true, cfg->nranks > 1, h->err));
     if (cfg->nranks > 1) {
         const char *why = nullptr;
         h->nccl = nccl_api(&why);

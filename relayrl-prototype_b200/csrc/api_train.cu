@@ -12,12 +12,14 @@ using namespace rrl;
 static int32_t allreduce_grad(rrl_learner *h, NetState &net)
 {
     if (h->cfg.nranks <= 1) return RRL_OK;
-    int rc = h->nccl->AllReduce(net.grad, net.grad, (size_t)net.dims.n_params(), NCCL_FLOAT32, NCCL_SUM, h->comm, h->stream);
+    // The sum over ranks is formed in float64 and rounded to f32 once, exactly like the single-GPU sum over CTAs
+    // (grad_reduce_kernel): N ranks and one rank then differ by float64 re-association only.  139 KB: latency-bound.
+    int rc = h->nccl->AllReduce(net.grad64, net.grad64, (size_t)net.dims.n_params(), NCCL_FLOAT64, NCCL_SUM, h->comm, h->stream);
     if (rc != 0) {
         h->err.set("ncclAllReduce(grad) failed: %s", h->nccl->GetErrorString(rc));
         return RRL_ENCCL;
     }
-    return RRL_OK;
+    return grad_round_launch(net, h->stream, h->err, &h->launches);
 }
 
 static TrainBuffers train_buffers(rrl_learner *h)

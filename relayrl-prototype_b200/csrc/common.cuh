@@ -75,6 +75,8 @@ struct NetState {
     NetDims dims;
     float *params;    // flat, torch order
     float *grad;      // flat gradient (after the CTA-partial reduction)
+    double *grad64;   // data parallel only: this rank's float64 gradient sum, all-reduced in float64 and rounded
+                      // to f32 once afterwards, so that N ranks and one rank differ by f64 re-association only
     float *m, *v;     // Adam moments
     double *partials64;     // [grid][n_params] per-CTA float64 gradient partials
     double *loss_partials;  // [grid][4]
@@ -93,6 +95,8 @@ int32_t policy_pass_launch(NetState &net, const TrainBuffers &tb, int logp_mode,
 int32_t value_pass_launch(NetState &net, const TrainBuffers &tb, bool with_grad, float *v_out,
                           cudaStream_t stream, ErrBuf &err, int *launches);
 // grad (already reduced, and all-reduced across ranks by the caller) -> Adam update of params (+ transposed copies)
+// grad64 (all-reduced) -> grad, one rounding
+int32_t grad_round_launch(NetState &net, cudaStream_t stream, ErrBuf &err, int *launches);
 int32_t adam_launch(NetState &net, double lr, double b1, double b2, double eps, cudaStream_t stream,
                     ErrBuf &err, int *launches);
 

@@ -77,6 +77,6 @@ namespace rrl {
 extern thread_local ErrBuf g_create_err;  // failures without a handle
 int32_t learner_flush_staging(rrl_learner *h);
 int32_t learner_finish(rrl_learner *h);
-int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, ErrBuf &err);
+int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bool data_parallel, ErrBuf &err);
 void net_free(NetState &net);
 }  // namespace rrl

@@ -507,6 +507,7 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tile_kernel(MlpArgs a)
 // grad[p] = sum over CTAs of the float64 partials, fixed order; losses likewise.
 __global__ void __launch_bounds__(256) grad_reduce_kernel(const double *__restrict__ partials, int grid_used,
                                                          int64_t n_params, float *__restrict__ grad,
+                                                         double *__restrict__ grad64,
                                                          const double *__restrict__ loss_partials,
                                                          double *__restrict__ loss_out)
 {
@@ -515,12 +516,19 @@ __global__ void __launch_bounds__(256) grad_reduce_kernel(const double *__restri
         double s = 0.0;
         for (int c = 0; c < grid_used; ++c) s += partials[(size_t)c * n_params + p];
         grad[p] = (float)s;
+        if (grad64) grad64[p] = s;
     }
     if (loss_partials && blockIdx.x == 0 && threadIdx.x < 4) {
         double s = 0.0;
         for (int c = 0; c < grid_used; ++c) s += loss_partials[(size_t)c * 4 + threadIdx.x];
         loss_out[threadIdx.x] = s;
     }
+}
+
+__global__ void __launch_bounds__(256) grad_round_kernel(const double *__restrict__ g64, float *__restrict__ g, int64_t n)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) g[i] = (float)g64[i];
 }
 
 // torch.optim.Adam, single-tensor CPU path, f32 with unfused operations:
@@ -597,7 +605,8 @@ int32_t run_pass(NetState &net, const TrainBuffers &tb, int mode, bool with_grad
     const int used = (int)std::min<int64_t>(grid, tiles);
     const int64_t P = nd.n_params();
     grad_reduce_kernel<<<(int)((P + 255) / 256), 256, 0, stream>>>(with_grad ? net.partials64 : nullptr, used, P,
-                                                                    net.grad, net.loss_partials, net.loss_out);
+                                                                    net.grad, with_grad ? net.grad64 : nullptr,
+                                                                    net.loss_partials, net.loss_out);
     RRL_CUDA_OK(cudaGetLastError(), err);
     if (launches) *launches += 2;
     return RRL_OK;
@@ -644,6 +653,15 @@ int32_t value_pass_launch(NetState &net, const TrainBuffers &tb, bool with_grad,
                           ErrBuf &err, int *launches)
 {
     return run_pass(net, tb, MODE_VALUE, with_grad, v_out, stream, err, launches);
+}
+
+int32_t grad_round_launch(NetState &net, cudaStream_t stream, ErrBuf &err, int *launches)
+{
+    const int64_t P = net.dims.n_params();
+    grad_round_kernel<<<(int)((P + 255) / 256), 256, 0, stream>>>(net.grad64, net.grad, P);
+    RRL_CUDA_OK(cudaGetLastError(), err);
+    if (launches) *launches += 1;
+    return RRL_OK;
 }
 
 int32_t adam_launch(NetState &net, double lr, double b1, double b2, double eps, cudaStream_t stream, ErrBuf &err,

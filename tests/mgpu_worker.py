@@ -26,9 +26,12 @@ def main():
     dist.broadcast(idt, 0)
     nccl_id = bytes(idt.cpu().tolist())
 
-    d, A, H, iters = 4, 2, 128, 2   # few Adam steps: later ones amplify float32-level differences (see below)
+    # the reference's defaults: 80 value iterations (src/sys_utils/config_loader.rs:68-78)
+    d, A, H, iters = 4, 2, 128, int(os.environ.get("MGPU_ITERS", "80"))
+    n_eps = int(os.environ.get("MGPU_EPISODES", "400"))     # 400 episodes ~ 120 k transitions; 28000 ~ 8 Mi
+    with_oracle = os.environ.get("MGPU_ORACLE", "1") == "1"
     rng = np.random.default_rng(21)
-    lens = rng.integers(1, 600, 400)
+    lens = rng.integers(1, 600, n_eps)
     offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
     n, E = int(offs[-1]), len(lens)
     obs = rng.standard_normal((n, d)).astype(np.float32)
@@ -79,18 +82,54 @@ def main():
             assert a["n_transitions"] == b["n_transitions"] == n and a["n_episodes"] == b["n_episodes"] == E
             for k in ("loss_pi", "kl", "entropy", "loss_v", "loss_v_old", "adv_mean", "adv_std"):
                 np.testing.assert_allclose(a[k], b[k], rtol=1e-5, atol=1e-7, err_msg=k)
-        # The all-reduce adds two ranks' f32 gradients where one rank sums everything in f64 first,
-        # i.e. the gradients differ at the 1e-7 level; Adam turns that into lr-sized differences on
-        # the parameters whose gradient is ~eps.  The reference shows the same sensitivity between
-        # MKL thread counts (tests/conftest.py), hence >= 99 % strict and everything within 0.1 lr.
-        for got, want, lr in ((pi_dp, S.get_params(0), 3e-4), (v_dp, S.get_params(1), 1e-3)):
-            err = np.abs(got - want)
-            frac = (err <= 5e-7 + 1e-5 * np.abs(want)).mean()
-            # two float32-level evaluations of the same epoch: the reference's own float32 run sits at
-            # 98.7 % strict agreement with its float64 run (tests/test_gpu_learner.py), so two of them
-            # may differ by about twice that
-            assert frac >= 0.97, "strict agreement %.4f" % frac
+        # Every rank sums its CTA partials in float64, NCCL adds the ranks in float64, and the result is rounded to
+        # f32 once -- the same construction as the single-GPU gradient, so the two runs differ by float64
+        # re-association and by where the 2048-row f32 accumulation windows fall (rank-local tiling).
+        def strict(a, b):
+            e = np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))
+            return float((e <= 5e-7 + 1e-5 * np.abs(b)).mean()), float(e.max())
+
+        for name, got, want, lr in (("policy", pi_dp, S.get_params(0), 3e-4), ("value", v_dp, S.get_params(1), 1e-3)):
+            frac, emax = strict(got, want)
+            print("MGPU %s vs 1 GPU: strict %.5f max abs err %.3g" % (name, frac, emax), flush=True)
+            assert frac >= 0.999, "%s: strict agreement with the 1-GPU run %.5f" % (name, frac)
             np.testing.assert_allclose(got, want, rtol=1e-5, atol=0.1 * lr)
+        if with_oracle:
+            # ... and against the oracle (the reference's arithmetic on the host): float32, and float64 as the
+            # tie-breaker -- the data-parallel result must be as close to the float64 truth as the reference is
+            torch.set_num_threads(8)
+            done = np.zeros(n + E, np.uint8)
+            rows = np.ones(n + E, bool)
+            mark = offs[1:] + np.arange(E)
+            done[mark], rows[mark] = 1, False
+
+            def widen(a, fill=0.0):
+                out = np.full((n + E,) + a.shape[1:], fill, a.dtype)
+                out[rows] = a
+                return out
+
+            rew_m = widen(rew)
+            rew_m[mark] = lvs
+            O = lo.OracleLearner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, seed=1)
+            O.ingest(widen(obs), widen(act), widen(mask, 1.0), rew_m, widen(val), widen(logp), done)
+            assert np.array_equal(np.asarray(O.offsets), offs)
+            data, _ = O.get()
+            pi_l, v_l = lo.unflatten(pi0, d, H, A), lo.unflatten(v0, d, H, 1)
+            ref = lo.train_epoch(pi_l, v_l, data, O.pi_lr, O.vf_lr, iters)
+            ref64 = lo.train_epoch([p.double() for p in pi_l], [p.double() for p in v_l],
+                                   {k: t.double() for k, t in data.items()}, O.pi_lr, O.vf_lr, iters)
+            a0 = res[0][0]
+            np.testing.assert_allclose(a0["loss_pi"], ref["LossPi"], rtol=1e-5, atol=1e-7)
+            np.testing.assert_allclose(a0["loss_v"], ref["LossV"], rtol=1e-5)
+            np.testing.assert_allclose(a0["loss_v_old"], ref["LossVOld"], rtol=1e-5)
+            for name, got, key, lr in (("policy", pi_dp, "pi_params", 3e-4), ("value", v_dp, "v_params", 1e-3)):
+                w32, w64 = lo.flatten(ref[key]).numpy(), lo.flatten(ref64[key]).numpy()
+                f_ref, m_ref = strict(w32, w64)
+                f_gpu, m_gpu = strict(got, w64)
+                print("MGPU %s vs float64 oracle: strict %.5f (float32 reference: %.5f), max %.3g (%.3g)"
+                      % (name, f_gpu, f_ref, m_gpu, m_ref), flush=True)
+                assert f_gpu >= min(f_ref, 0.999) - 1e-3, (name, f_gpu, f_ref)
+                np.testing.assert_allclose(got, w32, rtol=1e-5, atol=0.1 * lr)
         S.close()
         print("MGPU_OK world=%d n=%d" % (world, n))
     dist.barrier()
