@@ -38,12 +38,16 @@ def evaluate(pi_flat, v_flat, d, H, A, cols, adv, ret, n_global=None, dtype=torc
     pi = unflatten(pi_flat, d, H, A, dtype, dev)
     vf = unflatten(v_flat, d, H, 1, dtype, dev) if v_flat is not None else None
     acc = torch.zeros(4, dtype=torch.float64, device=dev)
+    mx = torch.zeros(3, dtype=torch.float64, device=dev)      # max |h1|, max |adv|, max |2 (v - ret)|
     for lo in range(0, n, chunk):
         hi = min(n, lo + chunk)
         obs = cols["obs"][lo:hi].to(dtype)
         mask = cols["mask"][lo:hi].to(dtype)
         act = cols["act"][lo:hi].long()
         logits = _mlp3(pi, obs) + (mask - 1) * 1e8
+        with torch.no_grad():
+            mx[0] = torch.maximum(mx[0], torch.relu(torch.nn.functional.linear(obs, pi[0], pi[1])).max().double())
+            mx[1] = torch.maximum(mx[1], adv[lo:hi].abs().max().double())
         logp = logits.gather(-1, act.unsqueeze(-1)).squeeze(-1)          # the RAW masked logit
         l_pi = -(logp * adv[lo:hi].to(dtype)).sum()
         l_pi.backward()
@@ -58,11 +62,20 @@ def evaluate(pi_flat, v_flat, d, H, A, cols, adv, ret, n_global=None, dtype=torc
             l_v = ((v - ret[lo:hi].to(dtype)) ** 2).sum()
             l_v.backward()
             acc[3] += l_v.detach().double()
+            with torch.no_grad():
+                mx[0] = torch.maximum(mx[0], torch.relu(torch.nn.functional.linear(obs, vf[0], vf[1])).max().double())
+                mx[2] = torch.maximum(mx[2], (2 * (v - ret[lo:hi].to(dtype))).abs().max().double())
         del obs, mask, logits, logp
     a = (acc / N).tolist()
-    out = {"loss_pi": a[0], "kl": a[1], "entropy": a[2],
+    m = mx.tolist()
+    # Largest change ONE (transition, hidden unit) pair can make to a W2-gradient entry: |dhead| |w3| |h1| / N.  A float32
+    # evaluation may take the other branch of a ReLU for a pre-activation within rounding of zero; each such flip moves
+    # gradient entries by up to this much, which at N = 2^20 .. 2^22 is above float32 rounding noise.
+    flip_pi = m[1] * float(pi[4].abs().max()) * m[0] / N
+    out = {"flip_bound_pi": flip_pi, "loss_pi": a[0], "kl": a[1], "entropy": a[2],
            "pi_grad": (torch.cat([p.grad.reshape(-1) for p in pi]).double() / N).cpu().numpy()}
     if vf is not None:
         out["loss_v"] = a[3]
+        out["flip_bound_v"] = m[2] * float(vf[4].abs().max()) * m[0] / N
         out["v_grad"] = (torch.cat([p.grad.reshape(-1) for p in vf]).double() / N).cpu().numpy()
     return out

@@ -4,9 +4,17 @@ same device buffers by plain torch (tests/f64_eval.py) -- SURVEY.md section 7's 
 CPU oracle would take hours.  What this pins that the small cases cannot: ~7 000 tiles per CTA, the 2048-row f32
 accumulation window spilling into the per-CTA float64 partials thousands of times, and 1/N at N = 2^22 .. 2^26.
 
-Criterion (the one of test_tc_gradients_many_tiles_vs_float64_autograd at 200x the size): losses rel 1e-5; each
-gradient at least as close to the float64 result as twice the distance of a float32 evaluation of the same formulas
-(torch, TF32 off), or 3e-6 of its largest entry, whichever is larger."""
+Criterion: losses rel 1e-5; each gradient is judged against the float64 result next to a float32 evaluation of the same
+formulas (torch, TF32 off): relative L2 error <= max(3e-5, twice the float32 evaluation's -- one ReLU flip is 1.2e-5 of
+the value gradient's norm at 4 Mi, a systematic accumulation error such as the tensor core's truncating adds would be
+>= 1e-4); 95th percentile of the
+entry-wise error <= max(twice the float32 evaluation's, 1e-6 of the largest entry); largest entry-wise error <= max(twice
+the float32 evaluation's, 3e-6 of the largest entry, four ReLU flips).  The percentile is there because the maximum is
+owned by ReLU flips, which touch < 1 % of the entries each.  A "ReLU flip": a float32 evaluation can land on the other side of zero for a
+pre-activation that float64 puts within rounding of it; one flipped (transition, unit) pair moves a gradient entry by up
+to |dhead| |w3| |h1| / N, which at N = 2^20 .. 2^22 exceeds float32 rounding noise (measured on B200: torch float32 and
+the CUDA-core kernel show the very same 7.45e-7 deviation at 1 Mi, the tensor-core kernel 7.1e-7 at 4 Mi, all of them
+8e-8 elsewhere; see gpurun log profiles/r2_gradscale.txt)."""
 import os
 import sys
 
@@ -81,10 +89,14 @@ def test_losses_and_gradients_vs_float64_at_bench_size(n):
     np.testing.assert_allclose(kl, r64["kl"], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(ent, r64["entropy"], rtol=1e-5, atol=1e-7)
     np.testing.assert_allclose(lv, r64["loss_v"], rtol=1e-5)
-    for name, got, key in (("policy", gp, "pi_grad"), ("value", gv, "v_grad")):
-        want, w32 = r64[key], r32[key]
-        e_gpu, e_ref, scale = np.abs(got - want).max(), np.abs(w32 - want).max(), np.abs(want).max()
-        print("n=%d %s gradient: max |err| vs float64 %.3g (torch float32: %.3g), largest entry %.3g"
-              % (n, name, e_gpu, e_ref, scale))
-        assert e_gpu <= max(2.0 * e_ref, 3e-6 * scale), (name, e_gpu, e_ref, scale)
-        np.testing.assert_allclose(got, want, rtol=1e-5, atol=max(2.0 * e_ref, 3e-6 * scale), err_msg=name)
+    for name, got, key, fkey in (("policy", gp, "pi_grad", "flip_bound_pi"), ("value", gv, "v_grad", "flip_bound_v")):
+        want, w32, flip = r64[key], r32[key], r64[fkey]
+        e_gpu, e_ref, scale = np.abs(got - want), np.abs(w32 - want), np.abs(want).max()
+        l2, l2_ref = np.linalg.norm(got - want) / np.linalg.norm(want), np.linalg.norm(w32 - want) / np.linalg.norm(want)
+        q_gpu, q_ref = np.quantile(e_gpu, 0.95), np.quantile(e_ref, 0.95)
+        print("n=%d %s gradient vs float64: max |err| %.3g (torch float32: %.3g), 95th percentile %.3g (%.3g), relative L2 "
+              "%.3g (%.3g); largest entry %.3g, one ReLU flip <= %.3g"
+              % (n, name, e_gpu.max(), e_ref.max(), q_gpu, q_ref, l2, l2_ref, scale, flip))
+        assert l2 <= max(3e-5, 2.0 * l2_ref), (name, l2, l2_ref)
+        assert q_gpu <= max(2.0 * q_ref, 1e-6 * scale), (name, q_gpu, q_ref, scale)
+        assert e_gpu.max() <= max(2.0 * e_ref.max(), 3e-6 * scale, 4.0 * flip), (name, e_gpu.max(), e_ref.max(), scale, flip)
