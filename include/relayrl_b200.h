@@ -33,6 +33,7 @@ extern "C" {
 #define RRL_ESTATE (-4)     /* call order violated (e.g. train before finish) */
 #define RRL_ENCCL (-5)      /* NCCL unavailable or failed */
 #define RRL_EFORMAT (-6)    /* malformed wire bytes (safetensors / pickle) */
+#define RRL_ENOMEM (-7)     /* host memory exhausted (no exception ever crosses this ABI) */
 
 /* element types of host payloads (wire dtypes, src/types/action.rs:92-101) */
 #define RRL_F32 0
@@ -159,6 +160,21 @@ int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, int32_t obs_d
                                    float *val, float *logp, uint8_t *done, int64_t cap, int64_t *count,
                                    char *errbuf, size_t errcap);
 
+/* ZMQ wire format: the bytes an agent PUSHes, serde_pickle::to_writer(&Vec<RelayRLAction>) (src/types/trajectory.rs:50-55),
+ * as TrainingServerZmq::_start_training_loop receives them (src/network/server/training_zmq.rs:994-1001).  Replaces
+ * pickle::from_slice + the JSON pipe + traj_from_json + receive_trajectory's per-action loop.  The decoder is a plain-data
+ * pickle reader (protocols 2-4; no globals, no reduce) that accepts serde's data model for these types under both
+ * encodings of Vec<u8> (list of ints / bytes), of unit variants (str / 1-tuple) and of newtype variants (1-entry dict /
+ * 2-tuple); anything else is RRL_EFORMAT.  All of the message is appended, or -- on any error -- none of it (the same
+ * holds for rrl_ingest_grpc_trajectory).  serde-pickle 1.2.0 itself is not in the reference tree: verified against
+ * Python's pickler on the equivalent object graphs, not against a live Rust peer. */
+int32_t rrl_ingest_pickle(rrl_learner_t *h, const uint8_t *msg, size_t len, int64_t *n_actions);
+/* The decoder alone, host only (same convention as rrl_decode_grpc_trajectory). */
+int32_t rrl_decode_pickle_trajectory(const uint8_t *msg, size_t len, int32_t obs_dim, int32_t act_dim,
+                                     int32_t with_baseline, float *obs, float *act, float *mask, float *rew,
+                                     float *val, float *logp, uint8_t *done, int64_t cap, int64_t *count,
+                                     char *errbuf, size_t errcap);
+
 /* ReplayBuffer.finish_path for every closed path of the epoch (replay_buffer.py:48-79) and
  * statistics_scalar over [0, ptr) (BaseReplayBuffer.py:30-53): one fused segmented reverse scan.
  * Returns this rank's counts. */
@@ -214,7 +230,7 @@ int32_t rrl_scan_device(const float *rew, const float *val, const int64_t *offse
  * its learner never touches a GPU).  Meant for hosts whose device-memory budget is fixed at
  * start-up -- a locked memory pool, a quota with no head-room, a plug-in inside an application
  * that forbids allocation calls after initialisation -- and which therefore cannot supply the
- * workspace rrl_scan_device wants.  The look-back descriptors live in a 557 312-byte array
+ * workspace rrl_scan_device wants.  The look-back descriptors live in a 393 472-byte array
  * compiled into the library (resident on every GPU that loads it, until the process exits), so
  * n_total is limited to RRL_SCAN_NOALLOC_MAX transitions; larger calls fail with RRL_EINVAL.
  * The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine.

@@ -119,6 +119,19 @@ int32_t learner_flush_staging(rrl_learner *h)
     return RRL_OK;
 }
 
+int32_t learner_mark(rrl_learner *h, LearnerMark &m)
+{
+    RRL_TRY(learner_flush_staging(h));  // nothing half-staged below the mark
+    m.ptr = h->ptr, m.n_offsets = h->offsets.size(), m.n_last_vals = h->last_vals.size(), m.finished = h->finished;
+    return RRL_OK;
+}
+
+void learner_rollback(rrl_learner *h, const LearnerMark &m)
+{
+    learner_flush_staging(h);  // rows staged since the mark land beyond it, where the buffer's contents mean nothing
+    h->ptr = m.ptr, h->offsets.resize(m.n_offsets), h->last_vals.resize(m.n_last_vals), h->finished = m.finished;
+}
+
 // Pack rows [i, j) of the batch (no terminal markers among them) into staging.
 static int32_t stage_rows(rrl_learner *h, const rrl_batch_view_t *b, int64_t i, int64_t j)
 {
@@ -244,6 +257,7 @@ const char *rrl_status_string(int32_t s)
         case RRL_ESTATE: return "invalid call order";
         case RRL_ENCCL: return "NCCL error";
         case RRL_EFORMAT: return "malformed wire data";
+        case RRL_ENOMEM: return "out of host memory";
         default: return "unknown status";
     }
 }

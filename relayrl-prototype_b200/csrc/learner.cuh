@@ -76,6 +76,14 @@ struct rrl_actor {
 namespace rrl {
 extern thread_local ErrBuf g_create_err;  // failures without a handle
 int32_t learner_flush_staging(rrl_learner *h);
+// all-or-nothing appends (wire decoders): where the replay buffer stood, and back to it
+struct LearnerMark {
+    int64_t ptr;
+    size_t n_offsets, n_last_vals;
+    bool finished;
+};
+int32_t learner_mark(rrl_learner *h, LearnerMark &m);
+void learner_rollback(rrl_learner *h, const LearnerMark &m);
 int32_t learner_finish(rrl_learner *h);
 int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bool data_parallel, ErrBuf &err);
 void net_free(NetState &net);

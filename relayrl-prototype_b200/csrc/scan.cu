@@ -10,85 +10,40 @@
 // replay_buffer.py:20-28); offsets int64 [E+1] are the successive path_start_idx values;
 // last_vals f32 [E] are the terminal markers' rewards (REINFORCE.py:86).
 //
-// Algorithm: both recurrences y[t] = x[t] + c*y[t+1] are affine maps of the value carried in
-// from the right; maps compose associatively, and an episode end resets the carry (the map's
-// slope becomes 0).  One pass over HBM (16 B/transition with baseline, 12 B without):
-//   persistent CTAs (cooperative launch), 2048-transition tiles taken right-to-left in a fixed
-//   stride; a producer warp prefetches the next tile while 8 consumer warps scan the current one
+// Algorithm: both recurrences y[t] = x[t] + c*y[t+1] are affine in the value carried in from the right, and an
+// episode end resets the carry.  Because c is a constant, the slope of any run of whole threads / warps / tiles
+// is a constant power of c (or 0 when a path ends inside it): only VALUES travel through shuffles, shared
+// memory and the tile descriptors.  One pass over HBM (16 B/transition with baseline, 12 B without):
+//   persistent CTAs taking 2048-transition tiles from a ticket counter, right-most first; a producer warp
+//   prefetches the next tile while 8 consumer warps scan the current one
 //     -> cp.async 16-byte copies into swizzled shared memory, blocked 8-per-thread reads
 //     -> episode ends of the tile found by a 32-ary warp search in `offsets`
-//     -> thread-serial map, warp-shuffle suffix scan, 8 warp maps through shared memory
+//     -> pass 1: thread-serial recurrences for a zero carry-in, the 16 results stay in registers
+//     -> warp-shuffle suffix scan of the values, 8 warp values through shared memory
 //     -> single-pass decoupled look-back across tiles (aggregate / inclusive descriptors whose
 //        64-bit words carry their own validity: no flags, no fences on the critical path)
-//     -> second thread-serial pass seeded with the carry, results staged through shared
-//        memory and written with coalesced 128-bit stores
-//     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64.
+//     -> pass 2: one FMA per result adds (power of c) x carry, rounds to f32, 128-bit streaming stores
+//        straight from registers
+//     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64, fixed summation order.
 // Arithmetic is float64 with float32 storage, as in the reference.
-#include <type_traits>
-
 #include "common.cuh"
 
 namespace rrl {
 
 namespace {
 
-#ifndef SCAN_CONSUMER_THREADS
-#define SCAN_CONSUMER_THREADS 256
-#endif
-#ifndef SCAN_MIN_CTAS
-#define SCAN_MIN_CTAS 2
-#endif
-constexpr int SCAN_THREADS = SCAN_CONSUMER_THREADS;
+constexpr int SCAN_THREADS = 256;                   // consumer threads (8 warps) ...
+constexpr int SCAN_CTA_THREADS = SCAN_THREADS + 32;  // ... + one producer warp
 constexpr int SCAN_VPT = 8;
-constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VPT;  // 2048 transitions per CTA
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_VPT;  // 2048 transitions per tile
 constexpr int SCAN_WARPS = SCAN_THREADS / 32;
 constexpr int SCAN_SMEM_FLOATS = SCAN_TILE + SCAN_TILE / 8 + 8;
+#ifndef SCAN_MIN_CTAS
+#define SCAN_MIN_CTAS 3
+#endif
 
-// 4 floats of padding after every 32: blocked 8-per-thread LDS.128 reads become conflict-free
+// 4 floats of padding after every 32: blocked 8-per-thread LDS.128 reads are conflict-free
 __device__ __forceinline__ int sidx(int j) { return j + ((j >> 5) << 2); }
-
-struct Map {  // ret: y = br + ar * carry ; adv: y = ba + aa * carry
-    double ar, br, aa, ba;
-};
-
-// left∘right: `right` is applied first (it is nearer the end of the episode)
-__device__ __forceinline__ Map compose(const Map &l, const Map &r)
-{
-    Map o;
-    o.ar = l.ar * r.ar;
-    o.br = fma(l.ar, r.br, l.br);
-    o.aa = l.aa * r.aa;
-    o.ba = fma(l.aa, r.ba, l.ba);
-    return o;
-}
-
-__device__ __forceinline__ Map shfl_down_map(const Map &m, int d)
-{
-    Map o;
-    o.ar = __shfl_down_sync(0xffffffffu, m.ar, d);
-    o.br = __shfl_down_sync(0xffffffffu, m.br, d);
-    o.aa = __shfl_down_sync(0xffffffffu, m.aa, d);
-    o.ba = __shfl_down_sync(0xffffffffu, m.ba, d);
-    return o;
-}
-__device__ __forceinline__ Map shfl_up_map(const Map &m, int d)
-{
-    Map o;
-    o.ar = __shfl_up_sync(0xffffffffu, m.ar, d);
-    o.br = __shfl_up_sync(0xffffffffu, m.br, d);
-    o.aa = __shfl_up_sync(0xffffffffu, m.aa, d);
-    o.ba = __shfl_up_sync(0xffffffffu, m.ba, d);
-    return o;
-}
-__device__ __forceinline__ Map shfl_map(const Map &m, int src)
-{
-    Map o;
-    o.ar = __shfl_sync(0xffffffffu, m.ar, src);
-    o.br = __shfl_sync(0xffffffffu, m.br, src);
-    o.aa = __shfl_sync(0xffffffffu, m.aa, src);
-    o.ba = __shfl_sync(0xffffffffu, m.ba, src);
-    return o;
-}
 
 // Tile descriptors carry their own validity: every 64-bit word starts as the sentinel 0xFFFF...F
 // (memset before the launch) and is written once with a single 64-bit store.  A reader polls the
@@ -105,103 +60,65 @@ __device__ __forceinline__ void st_relaxed2(double2 *p, double x, double y)
 {
     asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(x), "d"(y) : "memory");
 }
+__device__ __forceinline__ void st_stream4(float *p, float a, float b, float c, float d)
+{
+    asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
-// f32 <-> f64 by bit manipulation: the hardware conversion instructions (F2F.F64.F32 and back) issue
-// on the quarter-rate XU pipe, which the first version of this kernel saturated (95 % busy at 19 % of
-// HBM peak, profiles/r1_summary.md).  Zero, denormal, Inf and NaN take the slow instruction.
-// out of line on purpose: inlined, the compiler if-converts the rare branch and issues the slow
-// conversion for every element
-__device__ __noinline__ double f32_to_f64_slow(float x) { return (double)x; }
-__device__ __noinline__ float f64_to_f32_slow(double d) { return __double2float_rn(d); }
-
-__device__ __forceinline__ double f32_to_f64(float x)
-{
-    const unsigned u = __float_as_uint(x);
-    const unsigned a = u & 0x7fffffffu;
-    if (a - 0x00800000u >= 0x7f000000u && a != 0u) return f32_to_f64_slow(x);  // denormal / Inf / NaN (rare)
-    const unsigned hi = (u & 0x80000000u) | ((a >> 3) + 0x38000000u);
-    return __hiloint2double(a ? hi : u, u << 29);
-}
-// The same without the branch: right for zero and normal numbers; f32_needs_slow() says when it is not.  The scan
-// tests all 8 (16) inputs of a thread at once and takes ONE branch to a slow copy of the loop, instead of one
-// convergence barrier (BSSY/BRA/BSYNC) per conversion -- those were 16 % of the instruction stream.
-__device__ __forceinline__ bool f32_needs_slow(float x)
-{
-    const unsigned a = __float_as_uint(x) & 0x7fffffffu;
-    return a - 0x00800000u >= 0x7f000000u && a != 0u;
-}
-__device__ __forceinline__ double f32_to_f64_fast(float x)
-{
-    const unsigned u = __float_as_uint(x);
-    const unsigned a = u & 0x7fffffffu;
-    const unsigned hi = (u & 0x80000000u) | ((a >> 3) + 0x38000000u);
-    return __hiloint2double(a ? hi : u, u << 29);
-}
-// d rounded to 24 significant bits, still a double (Veltkamp split with 2^29 + 1)
-__device__ __forceinline__ double round_to_f32_precision(double d)
-{
-    // explicit _rn intrinsics: the compiler must not contract c - d into an FMA
-    const double c = __dmul_rn(d, 536870913.0);
-    return __dsub_rn(c, __dsub_rn(c, d));
-}
-// h = round_to_f32_precision(d): exact narrowing by bits when h is a normal f32, else the slow instruction on d
-__device__ __forceinline__ float narrow_f32(double h, double d)
-{
-    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
-    const unsigned t = hi - 0x38000000u;             // exponent rebased from 1023 to 127 (sign untouched)
-    if (((t << 1) >> 21) - 1u >= 254u) return f64_to_f32_slow(d);  // zero, f32-denormal range, overflow, Inf, NaN
-    return __uint_as_float((hi & 0x80000000u) | __funnelshift_l(lo, t, 3));
-}
-// branch-free form + its validity test (same convention as above; an exact zero is handled in the fast form)
-__device__ __forceinline__ bool narrow_needs_slow(double h)
-{
-    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
-    const unsigned t = hi - 0x38000000u;
-    return ((t << 1) >> 21) - 1u >= 254u && ((hi << 1) | lo) != 0u;
-}
-__device__ __forceinline__ float narrow_f32_fast(double h)
-{
-    const unsigned hi = (unsigned)__double2hiint(h), lo = (unsigned)__double2loint(h);
-    const unsigned bits = (hi & 0x80000000u) | __funnelshift_l(lo, hi - 0x38000000u, 3);
-    return __uint_as_float(((hi << 1) | lo) != 0u ? bits : (hi & 0x80000000u));
-}
+// f32 <-> f64 with the hardware conversions (F2F): exact for every input incl. denormals, Inf and NaN, and -- measured
+// on B200 with tools/cvt_rate.cu, profiles/r2_cvt_rate.txt -- 15 per clock per SM for both directions together, against
+// 9.8 for the integer-ALU widening the round-1 kernel used (7 instructions + the select for zero).  At five conversions
+// per transition that is 0.07 ms of the XU pipe for 64 Mi transitions, in parallel with the FP64 pipe and the loads.
+__device__ __forceinline__ double widen(float x) { return (double)x; }
+__device__ __forceinline__ float narrow(double x) { return __double2float_rn(x); }
 
 struct ScanArgs {
     const float *rew, *val;
     const int64_t *offsets;
     const float *last_vals;
-    int64_t n_ep;    // closed paths; the scan covers [0, offsets[n_ep]) (read on the device)
+    int64_t n_ep;     // closed paths; the scan covers [0, offsets[n_ep]) (read on the device)
+    int64_t n_total;  // size of the buffers: offsets[n_ep] beyond it is a caller error the kernel refuses to follow
     double gamma, gl;
-    double gamma_p, gl_p;  // gamma^SCAN_VPT, gl^SCAN_VPT: the slope of a thread's map when no path ends in its run
+    // powers of the two discounts (c = gamma for returns, gamma*lam for advantages), formed on the host by repeated
+    // multiplication: pw[j] = c^j (j = 0..8: an element k places from the right edge of its thread's run takes the
+    // run's carry times c^k); st[s] = c^(8 * 2^s) (slope of 2^s whole threads: the warp scan's steps); wp = c^256
+    // (one warp), tp = c^2048 (one tile)
+    double pw_r[SCAN_VPT + 1], pw_a[SCAN_VPT + 1];
+    double st_r[5], st_a[5];
+    double wp_r, wp_a, tp_r, tp_a;
     float *adv, *ret;
     // workspace
-    int *ticket;
-    int *flags;      // (reserved)
-    Map *agg;        // tile map (carry-in from the right -> value at the tile's first element)
-    double2 *incl;   // final (ret, adv) at the tile's first element
-    double2 *partials;
+    int *ticket;         // next logical tile (starts at -1: the memset that resets the descriptors covers it)
+    double2 *agg;        // open tile: value at its first element for a zero carry-in (its slope is tp)
+    double2 *incl;       // final (ret, adv) at the tile's first element
+    double2 *partials;   // per tile: (sum, sum of squares) of the f32-rounded advantages
 };
 
-// tile states published for the look-back
-
 // ---- persistent, warp-specialised tile pipeline ------------------------------------------------
-// A CTA is 8 consumer warps + 1 producer warp.  CTA c owns the logical tiles c, c+G, c+2G, ...
-// (logical tile j = physical tile num_tiles-1-j: right-most first); the launch is cooperative, so
-// all G CTAs are co-resident and the look-back can never wait on a CTA that is not running.
-// While the consumers work on tile j, the producer warp prepares tile j+G in the other buffer:
-// cp.async of rew/val into swizzled shared memory (the bytes in flight that keep HBM busy), the
-// 32-ary search for the tile's first path boundary, and the end-of-path bit mask + last_vals.
-constexpr int SCAN_CTA_THREADS = SCAN_THREADS + 32;
-
+// A CTA is 8 consumer warps + 1 producer warp and takes tiles from a ticket counter, right-most tile first, so every
+// tile a look-back can wait for has already been claimed by a CTA that is running: no co-residency requirement, no
+// cooperative launch, and the CTAs of an SM drift apart instead of hitting their barriers in lock-step.
+// While the consumers work on one tile the producer warp prepares the next one in the other buffer: cp.async of
+// rew/val into swizzled shared memory (the bytes in flight that keep HBM busy), the 32-ary search for the tile's
+// first path boundary, and the end-of-path bit mask + last_vals.
 struct TileBuf {
-    float r[SCAN_SMEM_FLOATS];   // rew in, adv out
-    float v[SCAN_SMEM_FLOATS];   // val in, ret out
+    float r[SCAN_SMEM_FLOATS];   // rew
+    float v[SCAN_SMEM_FLOATS];   // val (+ the first value of the next tile)
     float lv[SCAN_TILE];         // last_val at the positions where a path ends
     unsigned end[SCAN_TILE / 32];
     int tile;                    // physical tile index, -1 = no more work
     int pad[3];
 };
 static_assert(sizeof(TileBuf) % 16 == 0, "TileBuf must keep 16-byte alignment");
+
+struct ScanCtl {  // consumer hand-offs inside one tile
+    double2 wagg[SCAN_WARPS];      // per warp: value at its first element for a zero carry-in
+    double2 wcarry[SCAN_WARPS];    // per warp: the carry that enters it from the right (after the look-back)
+    double2 wstat[2][SCAN_WARPS];  // per warp: (sum, sum of squares); double buffered by tile parity
+    unsigned wclosed[SCAN_WARPS];  // per warp: a path ends inside it
+    double2 tpow[32];              // tp^i (ret, adv), i = 0..31: the look-back's per-lane slopes (set once per CTA)
+};
+constexpr double SCAN_CUT = 1e-100;
 
 __device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gmem_src, int src_bytes)
 {
@@ -210,10 +127,14 @@ __device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gme
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(SCAN_THREADS) : "memory"); }
 
-// producer warp: fill `B` for physical tile `tile` (or mark it empty)
+// producer warp: claim the next tile and fill `B` for it (or mark it empty)
 template <bool WB>
-__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan, int lane)
+__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int64_t n_scan, int num_tiles, int lane)
 {
+    int j = 0;
+    if (lane == 0) j = atomicAdd(a.ticket, 1) + 1;  // logical tile: 0 is the right-most
+    j = __shfl_sync(0xffffffffu, j, 0);
+    const int tile = j < num_tiles ? num_tiles - 1 - j : -1;
     if (lane == 0) B.tile = tile;
     if (tile < 0) return;
     for (int w = lane; w < SCAN_TILE / 32; w += 32) B.end[w] = 0u;
@@ -230,6 +151,10 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int 
     asm volatile("cp.async.commit_group;" ::: "memory");
     if (WB && lane == 0) B.v[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
 
+#ifdef SCAN_DBG_NO_SEARCH  // timing experiment only (wrong results)
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    return;
+#endif
     // first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0
     long long lo = 1, hi = a.n_ep;
     while (lo < hi) {
@@ -271,16 +196,17 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int 
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
-// consumer warps (threads 0..255): scan the tile in `B`, publish / look back, write the outputs
+// consumer warps (threads 0..255): scan the tile in `B`, publish / look back, write the outputs.
+// lane_r / lane_a: c^(8 * (31 - lane)), the slope between the warp's right edge and this lane's right edge.
 template <bool WB>
-__device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan,
-                                             int num_tiles, Map *wm_s, double *carry_s, double (*red_s)[2],
-                                             int tid)
+__device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan, int num_tiles,
+                                             ScanCtl &S, int tid, double lane_r, double lane_a, int parity)
 {
     const int lane = tid & 31, warp = tid >> 5;
-    float *r_s = B.r, *v_s = B.v;
+    const float *r_s = B.r, *v_s = B.v;
     const int64_t t0 = (int64_t)tile * SCAN_TILE;
     const int cnt = (int)min((int64_t)SCAN_TILE, n_scan - t0);
+    const bool full = cnt == SCAN_TILE;
 
     // ---- blocked reads: SCAN_VPT consecutive transitions per thread ---------------------------
     const int j0 = tid * SCAN_VPT;
@@ -296,223 +222,206 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
     }
     const float v_edge = WB ? v_s[sidx(j0 + SCAN_VPT)] : 0.f;
-    const unsigned eb = (B.end[j0 >> 5] >> (j0 & 31)) & 0xffu;
+    const unsigned eb = (B.end[j0 >> 5] >> (j0 & 31)) & 0xffu;  // bit k: a path ends at this thread's element k
     const bool open_right = ((B.end[(cnt - 1) >> 5] >> ((cnt - 1) & 31)) & 1u) == 0u;
+    const unsigned em = __ballot_sync(0xffffffffu, eb != 0u);  // lanes of this warp that hold a path end
 
-    // ---- pass 1: this thread's map; inputs are widened once and kept (rr = reward, dl = the
-    // GAE delta, both pure data) so that pass 2 is two DFMAs per transition ----------------------
-    // The widening is done branch-free; ONE test over all the thread's inputs sends a thread whose run holds a
-    // denormal, Inf or NaN to a copy of the loop that uses the exact (slow) conversion.
-    Map m;
-    double rr[SCAN_VPT], dl[WB ? SCAN_VPT : 1];
-    bool in_slow = WB && f32_needs_slow(v_edge);
-#pragma unroll
-    for (int k = 0; k < SCAN_VPT; ++k) in_slow |= f32_needs_slow(r[k]) || (WB && f32_needs_slow(v[k]));
-    auto pass1 = [&](auto slow_tag) {
-        constexpr bool SLOW = decltype(slow_tag)::value;
-        auto widen = [](float x) { return SLOW ? f32_to_f64(x) : f32_to_f64_fast(x); };
+    // ---- pass 1: the run's values for a zero carry-in, kept in registers ----------------------------------
+    // (float64 recurrences as the reference's lfilter calls, replay_buffer.py:63-77; pass 2 only adds the carry)
+    double lr[SCAN_VPT], la[SCAN_VPT];
+    {
         double ret_n = 0.0, adv_n = 0.0, v_n = WB ? widen(v_edge) : 0.0;
-        if (eb == 0u) {  // no path ends inside this thread's run (the common case)
+        if (em == 0u) {  // no path ends inside this warp's 256 transitions (warp-uniform)
 #pragma unroll
             for (int k = SCAN_VPT - 1; k >= 0; --k) {
-                rr[k] = widen(r[k]);
+                const double rr = widen(r[k]);
+                double dl = rr;
                 if (WB) {
                     const double vk = widen(v[k]);
-                    dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
+                    dl = fma(a.gamma, v_n, rr) - vk;
                     v_n = vk;
                 }
-                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
-                ret_n = fma(a.gamma, ret_n, rr[k]);
+                adv_n = fma(a.gl, adv_n, dl);
+                ret_n = fma(a.gamma, ret_n, rr);
+                la[k] = adv_n, lr[k] = ret_n;
             }
-            m.ar = a.gamma_p, m.aa = a.gl_p;
         } else {
-            double ar = 1.0, aa = 1.0;
 #pragma unroll
             for (int k = SCAN_VPT - 1; k >= 0; --k) {
                 if ((eb >> k) & 1u) {
                     // with baseline the marker's reward bootstraps both recurrences
                     // (replay_buffer.py:66-73); without it is ignored (replay_buffer.py:75-77)
-                    const double lvk = f32_to_f64(B.lv[j0 + k]);
+                    const double lvk = widen(B.lv[j0 + k]);
                     ret_n = WB ? lvk : 0.0;
                     adv_n = 0.0;
                     v_n = lvk;
-                    ar = 0.0;
-                    aa = 0.0;
                 }
-                rr[k] = widen(r[k]);
+                const double rr = widen(r[k]);
+                double dl = rr;
                 if (WB) {
                     const double vk = widen(v[k]);
-                    dl[k] = fma(a.gamma, v_n, rr[k]) - vk;
+                    dl = fma(a.gamma, v_n, rr) - vk;
                     v_n = vk;
                 }
-                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
-                ret_n = fma(a.gamma, ret_n, rr[k]);
-                ar *= a.gamma;
-                aa *= a.gl;
+                adv_n = fma(a.gl, adv_n, dl);
+                ret_n = fma(a.gamma, ret_n, rr);
+                la[k] = adv_n, lr[k] = ret_n;
             }
-            m.ar = ar, m.aa = aa;
         }
-        m.br = ret_n, m.ba = adv_n;
-    };
-    if (in_slow)
-        pass1(std::true_type{});
-    else
-        pass1(std::false_type{});
-
-    // ---- warp suffix scan of the maps (lane l: M_l∘M_{l+1}∘...∘M_31) ----------------------------
-    Map S = m;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const Map o = shfl_down_map(S, d);
-        if (lane + d < 32) S = compose(S, o);
     }
-    Map Ex = shfl_down_map(S, 1);  // maps of the lanes to the right of this one
-    if (lane == 31) Ex.ar = 1.0, Ex.br = 0.0, Ex.aa = 1.0, Ex.ba = 0.0;
-    if (lane == 0) wm_s[warp] = S;
-    consumer_sync();  // (also: every consumer has finished reading r_s / v_s)
 
-    Map Wsuf;  // maps of the warps to the right of this one
-    Wsuf.ar = 1.0, Wsuf.br = 0.0, Wsuf.aa = 1.0, Wsuf.ba = 0.0;
-    for (int w = warp + 1; w < SCAN_WARPS; ++w) Wsuf = compose(Wsuf, wm_s[w]);
+    // ---- warp suffix scan: sr/sa = value at this lane's first element for a zero carry into the warp ----------
+    // A step over d lanes multiplies by c^(8d) unless a path ends among the d lanes it bridges: the slope of an open
+    // run of whole threads is a constant, so only the two values travel (two 64-bit shuffles per step).
+    const unsigned above = em >> lane;                          // bit 0: this lane
+    const int dist = above ? __ffs(above) - 1 : 32;             // lanes from here to the first one holding a path end
+    double sr = lr[0], sa = la[0];
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+        const int d = 1 << s;
+        const double o_r = __shfl_down_sync(0xffffffffu, sr, d), o_a = __shfl_down_sync(0xffffffffu, sa, d);
+        if (lane + d < 32 && dist >= d) sr = fma(a.st_r[s], o_r, sr), sa = fma(a.st_a[s], o_a, sa);
+    }
+    double er = __shfl_down_sync(0xffffffffu, sr, 1), ea = __shfl_down_sync(0xffffffffu, sa, 1);  // the lanes to the right
+    if (lane == 31) er = 0.0, ea = 0.0;
+    const bool lane_open = (above >> 1) == 0u;  // no path ends to the right of this lane inside the warp
+    if (lane == 0) S.wagg[warp] = make_double2(sr, sa), S.wclosed[warp] = em;
+    consumer_sync();
 
-    // ---- publish the tile, fetch the carry from the tiles to the right -----------------------
+    // ---- warp 0: the eight warps, the tile's descriptor, the look-back -------------------------------------
     if (warp == 0) {
-        const Map T = compose(wm_s[0], Wsuf);
-        const bool closed = (T.ar == 0.0 && T.aa == 0.0);  // value at the tile's first element is final
-        if (lane == 0) {
-            if (closed) {
-                st_relaxed2(&a.incl[tile], T.br, T.ba);
-            } else {
-                double2 *ap = reinterpret_cast<double2 *>(&a.agg[tile]);
-                st_relaxed2(ap, T.ar, T.br);
-                st_relaxed2(ap + 1, T.aa, T.ba);
-            }
+        double xr = 0.0, xa = 0.0;
+        if (lane < SCAN_WARPS) xr = S.wagg[lane].x, xa = S.wagg[lane].y;
+        const unsigned cm = __ballot_sync(0xffffffffu, lane < SCAN_WARPS && S.wclosed[lane] != 0u);  // warps with a path end
+        const unsigned wabove = cm >> lane;
+        const int wdist = wabove ? __ffs(wabove) - 1 : 32;
+        double pr = a.wp_r, pa = a.wp_a;
+#pragma unroll
+        for (int d = 1; d < SCAN_WARPS; d <<= 1) {
+            const double o_r = __shfl_down_sync(0xffffffffu, xr, d), o_a = __shfl_down_sync(0xffffffffu, xa, d);
+            if (lane + d < SCAN_WARPS && wdist >= d) xr = fma(pr, o_r, xr), xa = fma(pa, o_a, xa);
+            pr *= pr, pa *= pa;
         }
-        double cr = 0.0, ca = 0.0;
-        if (open_right) {  // the right-most path of this tile continues in the next tile
-            Map acc;
-            acc.ar = 1.0, acc.br = 0.0, acc.aa = 1.0, acc.ba = 0.0;
+        // lane 0: the whole tile
+        const bool closed = cm != 0u;  // the value at the tile's first element does not depend on the carry-in
+        if (lane == 0) {
+            if (closed)
+                st_relaxed2(&a.incl[tile], xr, xa);
+            else
+                st_relaxed2(&a.agg[tile], xr, xa);
+        }
+        double cr = 0.0, ca = 0.0;  // carry into the tile from the tiles to the right
+#ifdef SCAN_DBG_NO_LOOKBACK  // timing experiment only (wrong results)
+        if (false) {
+#else
+        if (open_right) {          // the right-most path of this tile continues in the next tile
+#endif
+            const double lt_r = S.tpow[lane].x, lt_a = S.tpow[lane].y;  // tp^lane
+            double sc_r = 1.0, sc_a = 1.0;                               // tp^(32 * windows done)
             int base = tile + 1;
             while (true) {
                 const int k = base + lane;
-                Map q;
-                q.ar = 0.0, q.br = 0.0, q.aa = 0.0, q.ba = 0.0;
-                if (k < num_tiles) {
-                    const double2 *ap = reinterpret_cast<const double2 *>(&a.agg[k]);
+                double qr = 0.0, qa = 0.0;
+                bool final_value = true;  // beyond the last tile there is nothing to carry
+                // A tile whose slope towards this one has fallen below SCAN_CUT cannot change any f32 output: its
+                // value (<= 3.4e38 / (1 - c) for finite f32 inputs) times the slope is below 1e-56, eleven decades
+                // under the smallest f32 denormal.  Such lanes are not polled and end the look-back: with gamma = 0.98
+                // (tp = 1e-18) six tiles are read instead of every tile in flight to the right (up to ~440: the
+                // CTAs move in step, so their inclusive values appear together, late).
+                const bool needed = fmax(sc_r * lt_r, sc_a * lt_a) >= SCAN_CUT;
+                if (k < num_tiles && needed) {
                     while (true) {
                         const double2 iv = ld_relaxed2(&a.incl[k]);
                         if (!is_unset(iv.x) && !is_unset(iv.y)) {  // final value of that tile's first element
-                            q.br = iv.x, q.ba = iv.y;
+                            qr = iv.x, qa = iv.y;
                             break;
                         }
-                        const double2 lo2 = ld_relaxed2(ap), hi2 = ld_relaxed2(ap + 1);
-                        if (!is_unset(lo2.x) && !is_unset(lo2.y) && !is_unset(hi2.x) && !is_unset(hi2.y)) {
-                            q.ar = lo2.x, q.br = lo2.y, q.aa = hi2.x, q.ba = hi2.y;
+                        const double2 av = ld_relaxed2(&a.agg[k]);
+                        if (!is_unset(av.x) && !is_unset(av.y)) {  // an open tile: value for a zero carry-in, slope tp
+                            qr = av.x, qa = av.y, final_value = false;
                             break;
                         }
                     }
                 }
-                __syncwarp();
-                // ordered prefix over the window: P_l = q_0∘q_1∘...∘q_l
-                Map P = q;
+                const unsigned fin = __ballot_sync(0xffffffffu, final_value);
+                const int f = fin ? __ffs(fin) - 1 : 32;  // the window is used up to and including lane f
+                double wr = lane <= f ? qr * lt_r : 0.0, wa = lane <= f ? qa * lt_a : 0.0;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const Map o = shfl_up_map(P, d);
-                    if (lane >= d) P = compose(o, P);
+                for (int d = 16; d > 0; d >>= 1) {
+                    wr += __shfl_xor_sync(0xffffffffu, wr, d);
+                    wa += __shfl_xor_sync(0xffffffffu, wa, d);
                 }
-                const unsigned z = __ballot_sync(0xffffffffu, P.ar == 0.0 && P.aa == 0.0);
-                if (z != 0u) {
-                    const Map Ps = shfl_map(P, __ffs(z) - 1);
-                    const Map R = compose(acc, Ps);
-                    cr = R.br, ca = R.ba;
-                    break;
-                }
-                acc = compose(acc, shfl_map(P, 31));
+                cr = fma(sc_r, wr, cr), ca = fma(sc_a, wa, ca);
+                if (f < 32) break;
+                sc_r *= S.tpow[31].x * a.tp_r, sc_a *= S.tpow[31].y * a.tp_a;
                 base += 32;
             }
         }
-        if (lane == 0) {
-            if (!closed) st_relaxed2(&a.incl[tile], fma(T.ar, cr, T.br), fma(T.aa, ca, T.ba));
-            carry_s[0] = cr, carry_s[1] = ca;
+        if (lane == 0 && !closed) st_relaxed2(&a.incl[tile], fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
+        // carry into warp w: the warps to its right for a zero tile carry, plus the tile carry across them when open
+        double nr = __shfl_down_sync(0xffffffffu, xr, 1), na = __shfl_down_sync(0xffffffffu, xa, 1);
+        if (lane < SCAN_WARPS) {
+            if (lane == SCAN_WARPS - 1) nr = 0.0, na = 0.0;
+            if ((wabove >> 1) == 0u) {  // no path ends in the warps to the right of this one
+                double qr = 1.0, qa = 1.0;
+                for (int i = lane; i < SCAN_WARPS - 1; ++i) qr *= a.wp_r, qa *= a.wp_a;
+                nr = fma(qr, cr, nr), na = fma(qa, ca, na);
+            }
+            S.wcarry[lane] = make_double2(nr, na);
         }
     }
     consumer_sync();
 
-    // ---- pass 2: final values, seeded with the carry ------------------------------------------
-    // Same scheme for the narrowing: branch-free, one test over the thread's 16 results; a thread with a result
-    // in the f32-denormal range, an overflow, Inf or NaN redoes its run with the exact (slow) conversion.
+    // ---- pass 2: add the carry, round to f32, statistics, stores straight from registers -------------------------
     double s1 = 0.0, s2 = 0.0;
     {
-        const double wr = fma(Wsuf.ar, carry_s[0], Wsuf.br), wa = fma(Wsuf.aa, carry_s[1], Wsuf.ba);
-        const double ret0 = fma(Ex.ar, wr, Ex.br), adv0 = fma(Ex.aa, wa, Ex.ba);
+        double cr = er, ca = ea;
+        if (lane_open) {
+            const double2 wc = S.wcarry[warp];
+            cr = fma(lane_r, wc.x, cr), ca = fma(lane_a, wc.y, ca);
+        }
         float ao[SCAN_VPT], ro[SCAN_VPT];
-        auto pass2 = [&](auto slow_tag) -> bool {
-            constexpr bool SLOW = decltype(slow_tag)::value;
-            double ret_n = ret0, adv_n = adv0, t1 = 0.0, t2 = 0.0;
-            bool bad = false;
+        if (em == 0u && full) {
 #pragma unroll
-            for (int k = SCAN_VPT - 1; k >= 0; --k) {
-                if (eb != 0u && ((eb >> k) & 1u)) {
-                    ret_n = WB ? f32_to_f64(B.lv[j0 + k]) : 0.0;
-                    adv_n = 0.0;
-                }
-                adv_n = fma(a.gl, adv_n, WB ? dl[k] : rr[k]);
-                ret_n = fma(a.gamma, ret_n, rr[k]);
-                const double ha = round_to_f32_precision(adv_n), hr = round_to_f32_precision(ret_n);
-                double x;  // the f32-rounded advantage, as the reference's buffer holds it
-                if (SLOW) {
-                    ao[k] = narrow_f32(ha, adv_n), ro[k] = narrow_f32(hr, ret_n);
-                    x = f32_to_f64(ao[k]);
-                } else {
-                    bad |= narrow_needs_slow(ha) || narrow_needs_slow(hr);
-                    ao[k] = narrow_f32_fast(ha), ro[k] = narrow_f32_fast(hr);
-                    x = ha;  // ha is exactly that f32 value, widened
-                }
+            for (int k = 0; k < SCAN_VPT; ++k) {
+                ao[k] = narrow(fma(a.pw_a[SCAN_VPT - k], ca, la[k]));
+                ro[k] = narrow(fma(a.pw_r[SCAN_VPT - k], cr, lr[k]));
+                const double x = widen(ao[k]);  // the f32-rounded advantage, as the reference's buffer holds it
+                s1 += x;
+                s2 = fma(x, x, s2);
+            }
+        } else {
+            const int kmin = eb ? 32 - __clz(eb) : 0;  // elements at or left of the run's last path end take no carry
+#pragma unroll
+            for (int k = 0; k < SCAN_VPT; ++k) {
+                double ya = la[k], yr = lr[k];
+                if (k >= kmin) ya = fma(a.pw_a[SCAN_VPT - k], ca, ya), yr = fma(a.pw_r[SCAN_VPT - k], cr, yr);
+                ao[k] = narrow(ya), ro[k] = narrow(yr);
                 if (j0 + k < cnt) {
-                    t1 += x;
-                    t2 = fma(x, x, t2);
+                    const double x = widen(ao[k]);
+                    s1 += x;
+                    s2 = fma(x, x, s2);
                 }
             }
-            s1 = t1, s2 = t2;
-            return bad;
-        };
-        if (pass2(std::false_type{})) pass2(std::true_type{});
-        *reinterpret_cast<float4 *>(&r_s[sidx(j0)]) = make_float4(ao[0], ao[1], ao[2], ao[3]);
-        *reinterpret_cast<float4 *>(&r_s[sidx(j0) + 4]) = make_float4(ao[4], ao[5], ao[6], ao[7]);
-        *reinterpret_cast<float4 *>(&v_s[sidx(j0)]) = make_float4(ro[0], ro[1], ro[2], ro[3]);
-        *reinterpret_cast<float4 *>(&v_s[sidx(j0) + 4]) = make_float4(ro[4], ro[5], ro[6], ro[7]);
+        }
+        float *ap = a.adv + t0 + j0, *rp = a.ret + t0 + j0;
+        if (full || j0 + SCAN_VPT <= cnt) {
+            st_stream4(ap, ao[0], ao[1], ao[2], ao[3]);
+            st_stream4(ap + 4, ao[4], ao[5], ao[6], ao[7]);
+            st_stream4(rp, ro[0], ro[1], ro[2], ro[3]);
+            st_stream4(rp + 4, ro[4], ro[5], ro[6], ro[7]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < SCAN_VPT; ++k)
+                if (j0 + k < cnt) ap[k] = ao[k], rp[k] = ro[k];
+        }
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, d);
         s2 += __shfl_xor_sync(0xffffffffu, s2, d);
     }
-    if (lane == 0) red_s[warp][0] = s1, red_s[warp][1] = s2;
-    consumer_sync();
-
-    // ---- coalesced 128-bit stores -------------------------------------------------------------
-#pragma unroll
-    for (int c = tid; c < SCAN_TILE / 4; c += SCAN_THREADS) {
-        const int64_t g = t0 + 4 * c;
-        const float4 a4 = *reinterpret_cast<const float4 *>(&r_s[sidx(4 * c)]);
-        const float4 r4 = *reinterpret_cast<const float4 *>(&v_s[sidx(4 * c)]);
-        if (g + 3 < n_scan) {
-            __stcs(reinterpret_cast<float4 *>(a.adv + g), a4);
-            __stcs(reinterpret_cast<float4 *>(a.ret + g), r4);
-        } else {
-            const float *ap = &a4.x, *rp = &r4.x;
-            for (int k = 0; k < 4; ++k)
-                if (g + k < n_scan) {
-                    a.adv[g + k] = ap[k];
-                    a.ret[g + k] = rp[k];
-                }
-        }
-    }
-    if (tid == 0) {
-        double t1 = 0.0, t2 = 0.0;
-        for (int w = 0; w < SCAN_WARPS; ++w) t1 += red_s[w][0], t2 += red_s[w][1];
-        a.partials[tile] = make_double2(t1, t2);
-    }
+    if (lane == 0) S.wstat[parity][warp] = make_double2(s1, s2);
 }
 
 template <bool WB>
@@ -520,32 +429,42 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
 {
     extern __shared__ __align__(16) unsigned char scan_dyn[];
     TileBuf *buf = reinterpret_cast<TileBuf *>(scan_dyn);
-    __shared__ Map wm_s[SCAN_WARPS];
-    __shared__ double carry_s[2];
-    __shared__ double red_s[SCAN_WARPS][2];
+    __shared__ ScanCtl ctl;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const bool producer = tid >= SCAN_THREADS;
     const int64_t n_scan = a.offsets[a.n_ep];  // end of the last closed path
+    if (n_scan > a.n_total || n_scan < 0) return;  // inconsistent offsets: stats_reduce_kernel reports it (NaN statistics)
     const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
-    const int G = gridDim.x;
-    int j = blockIdx.x;  // logical tile; physical = num_tiles - 1 - j (right-most first)
 
-    if (producer) scan_prepare<WB>(a, buf[0], j < num_tiles ? num_tiles - 1 - j : -1, n_scan, lane);
+    double lane_r = 1.0, lane_a = 1.0;  // c^(8 * (31 - lane))
+    for (int i = lane; i < 31; ++i) lane_r *= a.st_r[0], lane_a *= a.st_a[0];
+
+    if (tid < 32) {
+        double tr = 1.0, ta = 1.0;
+        for (int i = 0; i < lane; ++i) tr *= a.tp_r, ta *= a.tp_a;
+        ctl.tpow[lane] = make_double2(tr, ta);
+    }
+    if (producer) scan_prepare<WB>(a, buf[0], n_scan, num_tiles, lane);
     __syncthreads();
-    int b = 0;
+    int b = 0, prev_tile = -1;
     while (true) {
         const int tile = buf[b].tile;
-        if (tile < 0) break;
-        if (producer) {
-            const int jn = j + G;
-            scan_prepare<WB>(a, buf[b ^ 1], jn < num_tiles ? num_tiles - 1 - jn : -1, n_scan, lane);
-        } else {
-            scan_consume<WB>(a, buf[b], tile, n_scan, num_tiles, wm_s, carry_s, red_s, tid);
+        // the previous tile's statistics: its eight warp sums in a fixed order (the result does not depend on which
+        // CTA took the tile)
+        if (tid == 0 && prev_tile >= 0) {
+            double t1 = 0.0, t2 = 0.0;
+            for (int w = 0; w < SCAN_WARPS; ++w) t1 += ctl.wstat[b ^ 1][w].x, t2 += ctl.wstat[b ^ 1][w].y;
+            a.partials[prev_tile] = make_double2(t1, t2);
         }
+        if (tile < 0) break;
+        if (producer)
+            scan_prepare<WB>(a, buf[b ^ 1], n_scan, num_tiles, lane);
+        else
+            scan_consume<WB>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b);
         __syncthreads();
+        prev_tile = tile;
         b ^= 1;
-        j += G;
     }
 }
 
@@ -570,9 +489,16 @@ __global__ void __launch_bounds__(1024) stats_reduce_kernel(const double2 *parti
                                                             int64_t n_total, double *stats, int finalize)
 {
     const int64_t n_scan = n_ep > 0 ? offsets[n_ep] : 0;
+    const int tid = threadIdx.x;
+    if (n_scan > n_total || n_scan < 0) {  // offsets that do not fit the buffers: the scan kernel refused to run
+        if (tid == 0) {
+            const double nan = __longlong_as_double(0x7ff8000000000000ll);
+            stats[0] = nan, stats[1] = nan, stats[2] = (double)n_total, stats[3] = nan, stats[4] = nan;
+        }
+        return;
+    }
     const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
     __shared__ double s_a[1024], s_b[1024];
-    const int tid = threadIdx.x;
     double a = 0.0, b = 0.0;
     for (int i = tid; i < num_tiles; i += 1024) {
         const double2 p = partials[i];
@@ -638,7 +564,7 @@ __global__ void __launch_bounds__(256) cvt_f64_f32_kernel(const double *__restri
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 struct WsLayout {
-    size_t ticket, flags, agg, incl, partials, total;
+    size_t ticket, agg, incl, partials, total;
     int num_tiles;
 };
 
@@ -649,8 +575,7 @@ WsLayout ws_layout(int64_t n)
     if (w.num_tiles < 1) w.num_tiles = 1;
     size_t o = 0;
     w.ticket = o, o += 256;
-    w.flags = o, o += align_up(sizeof(int) * (size_t)w.num_tiles, 256);
-    w.agg = o, o += align_up(sizeof(Map) * (size_t)w.num_tiles, 256);
+    w.agg = o, o += align_up(sizeof(double2) * (size_t)w.num_tiles, 256);
     w.incl = o, o += align_up(sizeof(double2) * (size_t)w.num_tiles, 256);
     w.partials = o, o += align_up(sizeof(double2) * (size_t)w.num_tiles, 256);
     w.total = o;
@@ -691,36 +616,54 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
     char *base = static_cast<char *>(workspace);
     ScanArgs a;
     a.rew = rew, a.val = val, a.offsets = offsets, a.last_vals = last_vals;
-    a.n_ep = n_ep;
+    a.n_ep = n_ep, a.n_total = n_total;
     a.gamma = gamma, a.gl = gamma * lam;  // the reference forms gamma * lam in double (replay_buffer.py:70)
-    a.gamma_p = 1.0, a.gl_p = 1.0;
-    for (int i = 0; i < SCAN_VPT; ++i) a.gamma_p *= a.gamma, a.gl_p *= a.gl;  // same products the serial path forms
+    // powers by repeated multiplication / squaring (the products a serial evaluation would form)
+    auto powers = [](double c, double *pw, double *st, double &wp, double &tp) {
+        pw[0] = 1.0;
+        for (int i = 1; i <= SCAN_VPT; ++i) pw[i] = pw[i - 1] * c;
+        st[0] = pw[SCAN_VPT];
+        for (int i = 1; i < 5; ++i) st[i] = st[i - 1] * st[i - 1];
+        wp = st[4] * st[4];                 // 32 threads
+        tp = wp;
+        for (int w = 1; w < SCAN_WARPS; w <<= 1) tp *= tp;  // 8 warps
+    };
+    static_assert(SCAN_WARPS == 8, "tp = wp^8 is formed by three squarings");
+    powers(a.gamma, a.pw_r, a.st_r, a.wp_r, a.tp_r);
+    powers(a.gl, a.pw_a, a.st_a, a.wp_a, a.tp_a);
     a.adv = adv, a.ret = ret;
     a.ticket = reinterpret_cast<int *>(base + w.ticket);
-    a.flags = reinterpret_cast<int *>(base + w.flags);
-    a.agg = reinterpret_cast<Map *>(base + w.agg);
+    a.agg = reinterpret_cast<double2 *>(base + w.agg);
     a.incl = reinterpret_cast<double2 *>(base + w.incl);
     a.partials = reinterpret_cast<double2 *>(base + w.partials);
     const int tiles = (int)((n_cover + SCAN_TILE - 1) / SCAN_TILE);
     if (tiles > 0) {
-        // every descriptor word starts as the "unset" sentinel
-        RRL_CUDA_OK(cudaMemsetAsync(base + w.agg, 0xFF, w.partials - w.agg, stream), err);
+        // every descriptor word starts as the "unset" sentinel; the same memset leaves the ticket counter at -1
+        RRL_CUDA_OK(cudaMemsetAsync(base, 0xFF, w.partials, stream), err);
         const size_t smem = 2 * sizeof(TileBuf);
-        const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
-                                       : reinterpret_cast<const void *>(scan_kernel<false>);
-        RRL_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
-        int dev = 0, sms = 0, per_sm = 0;
-        RRL_CUDA_OK(cudaGetDevice(&dev), err);
-        RRL_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), err);
-        RRL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SCAN_CTA_THREADS, smem), err);
-        if (per_sm < 1) {
-            err.set("scan: kernel does not fit on an SM (%zu B shared memory)", smem);
-            return RRL_ECUDA;
+        static int per_sm_cached[2] = {0, 0}, sms_cached = 0;
+        const int which = with_baseline ? 1 : 0;
+        if (per_sm_cached[which] == 0) {
+            const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
+                                           : reinterpret_cast<const void *>(scan_kernel<false>);
+            RRL_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
+            int dev = 0, sms = 0, per_sm = 0;
+            RRL_CUDA_OK(cudaGetDevice(&dev), err);
+            RRL_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev), err);
+            RRL_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, SCAN_CTA_THREADS, smem), err);
+            if (per_sm < 1) {
+                err.set("scan: kernel does not fit on an SM (%zu B shared memory)", smem);
+                return RRL_ECUDA;
+            }
+            sms_cached = sms, per_sm_cached[which] = per_sm;
         }
-        // co-resident by construction: the look-back spins on tiles owned by other CTAs
-        const int grid = std::min(tiles, per_sm * sms);
-        void *args[] = {&a};
-        RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SCAN_CTA_THREADS), args, smem, stream), err);
+        // persistent CTAs, as many as fit; tiles come from the ticket counter, so nothing depends on co-residency
+        const int grid = std::min(tiles, per_sm_cached[which] * sms_cached);
+        if (with_baseline)
+            scan_kernel<true><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a);
+        else
+            scan_kernel<false><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a);
+        RRL_CUDA_OK(cudaGetLastError(), err);
         if (launches) *launches += 1;
     }
     if (stats_out) {
@@ -784,7 +727,7 @@ int32_t cvt_f64_f32_launch(const double *src, float *dst, int64_t n, cudaStream_
 // initialisation.  rrl_scan_device() asks such callers for a workspace they cannot produce.
 //
 // Here the tile descriptors of the single-pass look-back live in a fixed array that is part of
-// the library image: every GPU that loads librelayrl_b200.so carries these 557 312 bytes until
+// the library image: every GPU that loads librelayrl_b200.so carries these 393 472 bytes until
 // the process exits.  That bounds the size: at most RRL_SCAN_NOALLOC_MAX transitions per call.
 // ---------------------------------------------------------------------------------------------
 #include <mutex>
@@ -794,12 +737,10 @@ extern thread_local ErrBuf g_create_err;
 
 namespace {
 constexpr int64_t NOALLOC_MAX_TILES = RRL_SCAN_NOALLOC_MAX / SCAN_TILE;  // 8192
-// ticket (256) + flags + aggregates + inclusive values + statistic partials, each 256-aligned
-constexpr size_t NOALLOC_WS_BYTES = 256 + NOALLOC_MAX_TILES * (sizeof(int) + sizeof(Map) + 2 * sizeof(double2));
+// ticket (256) + aggregates + inclusive values + statistic partials, each 256-aligned
+constexpr size_t NOALLOC_WS_BYTES = 256 + NOALLOC_MAX_TILES * 3 * sizeof(double2);
 static_assert(RRL_SCAN_NOALLOC_MAX % SCAN_TILE == 0, "limit must be a whole number of tiles");
-#if SCAN_CONSUMER_THREADS == 256
-static_assert(NOALLOC_WS_BYTES == 557312, "documented size of the static scratch");
-#endif
+static_assert(NOALLOC_WS_BYTES == 393472, "documented size of the static scratch");
 
 static __device__ __align__(256) unsigned char g_scan_scratch[NOALLOC_WS_BYTES];
 

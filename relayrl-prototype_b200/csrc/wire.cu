@@ -12,17 +12,11 @@
 #include <thread>
 #include <vector>
 
-#include "learner.cuh"
+#include "wire.h"
 
 namespace rrl {
 
-struct BlobView {
-    int dtype;  // 0 F32, 1 F64, 2 I64, 3 I32, 4 U8/BOOL
-    const uint8_t *data;
-    size_t nbytes;
-    size_t count;
-};
-
+// bounded helpers: the header is network bytes without a terminator
 static const char *find_key(const char *hdr, size_t n, const char *key)
 {
     const size_t kl = strlen(key);
@@ -30,8 +24,26 @@ static const char *find_key(const char *hdr, size_t n, const char *key)
         if (memcmp(hdr + i, key, kl) == 0) return hdr + i + kl;
     return nullptr;
 }
+static bool starts_with(const char *p, const char *end, const char *lit)
+{
+    const size_t n = strlen(lit);
+    return (size_t)(end - p) >= n && memcmp(p, lit, n) == 0;
+}
+// unsigned decimal at p (at least one digit, no overflow past 2^63); advances p
+static bool rd_uint(const char *&p, const char *end, unsigned long long &v)
+{
+    const char *q = p;
+    v = 0;
+    while (q < end && *q >= '0' && *q <= '9') {
+        if (v > (~0ull >> 1) / 10) return false;
+        v = v * 10 + (unsigned)(*q++ - '0');
+    }
+    if (q == p) return false;
+    p = q;
+    return true;
+}
 
-static int32_t parse_blob(const uint8_t *blob, size_t len, BlobView &out, ErrBuf &err)
+int32_t parse_blob(const uint8_t *blob, size_t len, BlobView &out, ErrBuf &err)
 {
     if (!blob || len < 8) {
         err.set("safetensors blob shorter than its length prefix");
@@ -47,30 +59,58 @@ static int32_t parse_blob(const uint8_t *blob, size_t len, BlobView &out, ErrBuf
     const char *end = hdr + hl;
     const char *dt = find_key(hdr, hl, "\"dtype\":\"");
     const char *off = find_key(hdr, hl, "\"data_offsets\":[");
-    if (!dt || !off) {
-        err.set("safetensors header lacks dtype / data_offsets");
+    const char *shp = find_key(hdr, hl, "\"shape\":[");
+    if (!dt || !off || !shp) {
+        err.set("safetensors header lacks dtype / shape / data_offsets");
         return RRL_EFORMAT;
     }
     size_t esz;
-    if (!strncmp(dt, "F64", 3)) out.dtype = 1, esz = 8;
-    else if (!strncmp(dt, "F32", 3)) out.dtype = 0, esz = 4;
-    else if (!strncmp(dt, "I64", 3)) out.dtype = 2, esz = 8;
-    else if (!strncmp(dt, "I32", 3)) out.dtype = 3, esz = 4;
-    else if (!strncmp(dt, "U8", 2) || !strncmp(dt, "BOOL", 4)) out.dtype = 4, esz = 1;
+    if (starts_with(dt, end, "F64\"")) out.dtype = 1, esz = 8;
+    else if (starts_with(dt, end, "F32\"")) out.dtype = 0, esz = 4;
+    else if (starts_with(dt, end, "I64\"")) out.dtype = 2, esz = 8;
+    else if (starts_with(dt, end, "I32\"")) out.dtype = 3, esz = 4;
+    else if (starts_with(dt, end, "I16\"")) out.dtype = 5, esz = 2;
+    else if (starts_with(dt, end, "U8\"") || starts_with(dt, end, "BOOL\"")) out.dtype = 4, esz = 1;
     else {
-        err.set("safetensors dtype %.4s unsupported", dt);
+        err.set("safetensors dtype %.*s unsupported", (int)std::min<size_t>(4, (size_t)(end - dt)), dt);
         return RRL_EFORMAT;
     }
-    char *p = nullptr;
-    const unsigned long long b0 = strtoull(off, &p, 10);
-    if (!p || p >= end || *p != ',') {
+    unsigned long long b0 = 0, b1 = 0;
+    if (!rd_uint(off, end, b0) || off >= end || *off != ',' || !rd_uint(++off, end, b1) || off >= end || *off != ']') {
         err.set("safetensors data_offsets malformed");
         return RRL_EFORMAT;
     }
-    const unsigned long long b1 = strtoull(p + 1, &p, 10);
+    // shape: [] (a scalar, one element) or [n0, n1, ...]
+    unsigned long long numel = 1;
+    while (shp < end && *shp == ' ') ++shp;
+    if (shp < end && *shp != ']') {
+        while (true) {
+            unsigned long long dim = 0;
+            while (shp < end && *shp == ' ') ++shp;
+            if (!rd_uint(shp, end, dim) || (dim != 0 && numel > (1ull << 40) / dim)) {
+                err.set("safetensors shape malformed");
+                return RRL_EFORMAT;
+            }
+            numel *= dim;
+            while (shp < end && *shp == ' ') ++shp;
+            if (shp < end && *shp == ',') {
+                ++shp;
+                continue;
+            }
+            break;
+        }
+    }
+    if (shp >= end || *shp != ']') {
+        err.set("safetensors shape malformed");
+        return RRL_EFORMAT;
+    }
     const size_t payload = len - 8 - hl;
     if (b1 < b0 || b1 > payload || (b1 - b0) % esz) {
         err.set("safetensors data_offsets [%llu,%llu] outside payload of %zu bytes", b0, b1, payload);
+        return RRL_EFORMAT;
+    }
+    if (numel * esz != b1 - b0) {
+        err.set("safetensors shape holds %llu elements but data_offsets span %llu bytes", numel, b1 - b0);
         return RRL_EFORMAT;
     }
     out.data = blob + 8 + hl + b0;
@@ -79,13 +119,14 @@ static int32_t parse_blob(const uint8_t *blob, size_t len, BlobView &out, ErrBuf
     return RRL_OK;
 }
 
-static float blob_at(const BlobView &b, size_t i)
+float blob_at(const BlobView &b, size_t i)
 {
     switch (b.dtype) {
         case 0: { float v; memcpy(&v, b.data + 4 * i, 4); return v; }
         case 1: { double v; memcpy(&v, b.data + 8 * i, 8); return (float)v; }  // f64 -> f32 as numpy's store does
         case 2: { int64_t v; memcpy(&v, b.data + 8 * i, 8); return (float)v; }
         case 3: { int32_t v; memcpy(&v, b.data + 4 * i, 4); return (float)v; }
+        case 5: { int16_t v; memcpy(&v, b.data + 2 * i, 2); return (float)v; }
         default: return (float)b.data[i];
     }
 }
@@ -221,11 +262,6 @@ static int32_t parse_data_value(const char *js, size_t n, std::vector<uint8_t> &
     return RRL_OK;
 }
 
-struct HostColumns {
-    float *obs, *act, *mask, *rew, *val, *logp;
-    uint8_t *done;
-    int64_t cap;
-};
 
 // One action sub-message -> row r of the columns.  Returns RRL_OK or RRL_EFORMAT with `err` set.
 static int32_t decode_grpc_action(Cur act, int64_t r, int d, int A, bool with_baseline, const HostColumns &o,
@@ -310,16 +346,15 @@ truncated:
     return RRL_EFORMAT;
 }
 
-// Decodes one serialized Trajectory into SoA rows (terminal markers become rows with done = 1 that carry only
-// their reward, as rrl_batch_view_t expects).  Two passes: the top-level fields are walked once to index the
-// action sub-messages (cheap: one varint pair each), then the actions -- ~420 B of safetensors blobs and ~500 B of
-// JSON byte arrays apiece, the expensive part -- are decoded independently, on several host threads when the
-// message is large.  On failure the error of the lowest-numbered bad action is reported, as a serial decoder would.
-static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int A, bool with_baseline, const HostColumns &o,
-                                      int64_t &count, ErrBuf &err)
+// A serialized Trajectory is decoded in two passes.  index_grpc_actions walks the top-level fields once (cheap: one
+// varint pair per action) and returns the action sub-messages -- so the caller knows the row count BEFORE it sizes
+// anything.  decode_grpc_actions then decodes the actions -- ~420 B of safetensors blobs and ~500 B of JSON byte arrays
+// apiece, the expensive part -- independently into SoA rows (terminal markers become rows with done = 1 that carry
+// only their reward, as rrl_batch_view_t expects), on several host threads when the message is large.  On failure the
+// error of the lowest-numbered bad action is reported, as a serial decoder would.
+static int32_t index_grpc_actions(const uint8_t *msg, size_t len, std::vector<Cur> &actions, ErrBuf &err)
 {
-    count = 0;
-    std::vector<Cur> actions;
+    actions.clear();
     Cur top{msg, msg + len};
     while (top.p < top.end) {
         uint64_t key;
@@ -331,6 +366,13 @@ static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int
         }
         if (key == ((1u << 3) | 2u)) actions.push_back(sub);
     }
+    return RRL_OK;
+}
+
+static int32_t decode_grpc_actions(const std::vector<Cur> &actions, int d, int A, bool with_baseline, const HostColumns &o,
+                                   int64_t &count, ErrBuf &err)
+{
+    count = 0;
     const int64_t n = (int64_t)actions.size();
     if (n > o.cap) {
         err.set("trajectory holds %lld actions, more than the %lld rows the caller provided", (long long)n, (long long)o.cap);
@@ -342,14 +384,22 @@ static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int
     std::vector<int32_t> status(nthreads, RRL_OK);
     std::vector<ErrBuf> errs(nthreads);
     auto work = [&](int t) {
-        std::vector<uint8_t> scratch;
-        scratch.reserve(256);
-        const int64_t lo = n * t / nthreads, hi = n * (t + 1) / nthreads;
-        for (int64_t r = lo; r < hi; ++r) {
-            const int32_t st = decode_grpc_action(actions[(size_t)r], r, d, A, with_baseline, o, scratch, errs[t]);
-            if (st != RRL_OK) {
-                status[t] = st;
-                return;  // later actions of this range are not needed: the call fails
+        try {
+            std::vector<uint8_t> scratch;
+            scratch.reserve(256);
+            const int64_t lo = n * t / nthreads, hi = n * (t + 1) / nthreads;
+            for (int64_t r = lo; r < hi; ++r) {
+                const int32_t st = decode_grpc_action(actions[(size_t)r], r, d, A, with_baseline, o, scratch, errs[t]);
+                if (st != RRL_OK) {
+                    status[t] = st;
+                    return;  // later actions of this range are not needed: the call fails
+                }
+            }
+        } catch (...) {  // nothing may escape a worker thread (std::terminate) or the C ABI
+            status[t] = RRL_ENOMEM;
+            try {
+                errs[t].set("gRPC trajectory decode: out of host memory");
+            } catch (...) {
             }
         }
     };
@@ -357,8 +407,13 @@ static int32_t decode_grpc_trajectory(const uint8_t *msg, size_t len, int d, int
         work(0);
     } else {
         std::vector<std::thread> pool;
-        for (int t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
+        int started = 1;
+        try {
+            for (int t = 1; t < nthreads; ++t, ++started) pool.emplace_back(work, t);
+        } catch (...) {  // the system refused another thread: the rest of the ranges run here
+        }
         work(0);
+        for (int t = started; t < nthreads; ++t) work(t);
         for (auto &th : pool) th.join();
     }
     for (int t = 0; t < nthreads; ++t)  // ranges are in action order: the first failing range holds the first bad action
@@ -380,6 +435,7 @@ extern "C" int32_t rrl_ingest_wire_action(rrl_learner_t *h, const uint8_t *obs_b
                                           const uint8_t *logp_blob, size_t logp_len, uint8_t done)
 {
     if (!h) return RRL_EINVAL;
+    return abi_guard(h->err, "rrl_ingest_wire_action", [&]() -> int32_t {
     rrl_batch_view_t b;
     memset(&b, 0, sizeof b);
     uint8_t dn = done ? 1 : 0;
@@ -413,6 +469,7 @@ extern "C" int32_t rrl_ingest_wire_action(rrl_learner_t *h, const uint8_t *obs_b
     b.obs = obs.data(), b.act = &act, b.mask = mask.data(), b.rew = &rew, b.val = &val, b.logp = &logp, b.done = &dn;
     b.count = 1, b.obs_dtype = RRL_F32, b.mask_dtype = RRL_F32;
     return rrl_ingest_packed(h, &b);
+    });
 }
 
 extern "C" int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, int32_t obs_dim, int32_t act_dim, int32_t with_baseline,
@@ -423,7 +480,11 @@ extern "C" int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, in
         return RRL_EINVAL;
     ErrBuf err;
     const HostColumns o{obs, act, mask, rew, val, logp, done, cap};
-    const int32_t st = decode_grpc_trajectory(msg, len, obs_dim, act_dim, with_baseline != 0, o, *count, err);
+    const int32_t st = abi_guard(err, "rrl_decode_grpc_trajectory", [&]() -> int32_t {
+        std::vector<Cur> actions;
+        RRL_TRY(index_grpc_actions(msg, len, actions, err));
+        return decode_grpc_actions(actions, obs_dim, act_dim, with_baseline != 0, o, *count, err);
+    });
     if (st != RRL_OK && errbuf && errcap) {
         strncpy(errbuf, err.msg.c_str(), errcap - 1);
         errbuf[errcap - 1] = 0;
@@ -434,19 +495,39 @@ extern "C" int32_t rrl_decode_grpc_trajectory(const uint8_t *msg, size_t len, in
 extern "C" int32_t rrl_ingest_grpc_trajectory(rrl_learner_t *h, const uint8_t *msg, size_t len, int64_t *n_actions)
 {
     if (!h || (!msg && len)) return RRL_EINVAL;
-    const int d = h->cfg.obs_dim, A = h->cfg.act_dim;
-    // an action costs at least 2 bytes on the wire (tag + length): that bounds the row count
-    const int64_t cap = (int64_t)(len / 2) + 1;
-    std::vector<float> obs((size_t)cap * d), mask((size_t)cap * A), act(cap), rew(cap), val(cap), logp(cap);
-    std::vector<uint8_t> done(cap);
-    const HostColumns o{obs.data(), act.data(), mask.data(), rew.data(), val.data(), logp.data(), done.data(), cap};
-    int64_t count = 0;
-    RRL_TRY(decode_grpc_trajectory(msg, len, d, A, h->cfg.with_baseline != 0, o, count, h->err));
-    if (n_actions) *n_actions = count;
-    if (count == 0) return RRL_OK;
-    rrl_batch_view_t b;
-    memset(&b, 0, sizeof b);
-    b.obs = obs.data(), b.act = act.data(), b.mask = mask.data(), b.rew = rew.data(), b.val = val.data(), b.logp = logp.data();
-    b.done = done.data(), b.count = count, b.obs_dtype = RRL_F32, b.mask_dtype = RRL_F32;
-    return rrl_ingest_packed(h, &b);
+    return abi_guard(h->err, "rrl_ingest_grpc_trajectory", [&]() -> int32_t {
+        const int d = h->cfg.obs_dim, A = h->cfg.act_dim;
+        // index pass first: the host rows are sized from the action count (never from the byte length), in chunks of
+        // at most INGEST_CHUNK_ROWS so that a huge or hostile message cannot ask for gigabytes; a failure in a later
+        // chunk rolls the buffer back to where it stood (all of the message is appended, or none of it)
+        std::vector<Cur> actions;
+        RRL_TRY(index_grpc_actions(msg, len, actions, h->err));
+        const int64_t n = (int64_t)actions.size();
+        if (n_actions) *n_actions = n;
+        if (n == 0) return RRL_OK;
+        LearnerMark mark;
+        RRL_TRY(learner_mark(h, mark));
+        OwnedColumns cols(std::min<int64_t>(n, INGEST_CHUNK_ROWS), d, A);
+        std::vector<Cur> part;
+        for (int64_t lo = 0; lo < n; lo += INGEST_CHUNK_ROWS) {
+            const int64_t hi = std::min<int64_t>(n, lo + INGEST_CHUNK_ROWS);
+            part.assign(actions.begin() + lo, actions.begin() + hi);
+            int64_t count = 0;
+            int32_t st = decode_grpc_actions(part, d, A, h->cfg.with_baseline != 0, cols.view, count, h->err);
+            if (st == RRL_OK) {
+                rrl_batch_view_t b;
+                memset(&b, 0, sizeof b);
+                b.obs = cols.view.obs, b.act = cols.view.act, b.mask = cols.view.mask, b.rew = cols.view.rew, b.val = cols.view.val;
+                b.logp = cols.view.logp, b.done = cols.view.done, b.count = count, b.obs_dtype = RRL_F32, b.mask_dtype = RRL_F32;
+                st = rrl_ingest_packed(h, &b);
+            }
+            if (st != RRL_OK) {
+                const std::string why = h->err.msg;
+                learner_rollback(h, mark);
+                h->err.msg = why;
+                return st;
+            }
+        }
+        return RRL_OK;
+    });
 }

@@ -67,6 +67,9 @@ SIGNATURES = {
     "rrl_ingest_grpc_trajectory": (C.c_int32, [_P, _P, C.c_size_t, C.POINTER(C.c_int64)]),
     "rrl_decode_grpc_trajectory": (C.c_int32, [_P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P, _P,
                                                C.c_int64, C.POINTER(C.c_int64), C.c_char_p, C.c_size_t]),
+    "rrl_ingest_pickle": (C.c_int32, [_P, _P, C.c_size_t, C.POINTER(C.c_int64)]),
+    "rrl_decode_pickle_trajectory": (C.c_int32, [_P, C.c_size_t, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P, _P, _P, _P, _P,
+                                                 C.c_int64, C.POINTER(C.c_int64), C.c_char_p, C.c_size_t]),
     "rrl_finish": (C.c_int32, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "rrl_get_offsets": (C.c_int32, [_P, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "rrl_get_returns": (C.c_int32, [_P, _P, C.c_int64]),

@@ -149,6 +149,13 @@ class Learner:
         self._ck(self._L.rrl_ingest_grpc_trajectory(self._h, msg, len(msg), C.byref(n)))
         return n.value
 
+    def ingest_pickle(self, msg):
+        """One ZMQ trajectory message: serde-pickle of Vec<RelayRLAction> (src/types/trajectory.rs:50-55,
+        src/network/server/training_zmq.rs:994-1001); returns the number of actions it held."""
+        n = C.c_int64()
+        self._ck(self._L.rrl_ingest_pickle(self._h, msg, len(msg), C.byref(n)))
+        return n.value
+
     # -- finish_path for every closed path + statistics (replay_buffer.py:48-79) ------------------
     def finish(self):
         n, e = C.c_int64(), C.c_int64()
@@ -304,16 +311,25 @@ def normalise_device(adv, n, stats, out, stream=None):
                                           C.c_void_p(stream) if stream else None))
 
 
+def decode_pickle_trajectory(msg, obs_dim, act_dim, with_baseline, cap=None):
+    """Host-only decode of a serde-pickle Vec<RelayRLAction> (the ZMQ transport's message) into SoA f32 columns."""
+    return _decode(_lib.lib().rrl_decode_pickle_trajectory, msg, obs_dim, act_dim, with_baseline, cap)
+
+
 def decode_grpc_trajectory(msg, obs_dim, act_dim, with_baseline, cap=None):
     """Host-only decode of a serialized proto Trajectory into SoA f32 columns (rrl_batch_view_t convention:
     a terminal marker is a row with done = 1 that carries only its reward).  Needs no GPU."""
+    return _decode(_lib.lib().rrl_decode_grpc_trajectory, msg, obs_dim, act_dim, with_baseline, cap)
+
+
+def _decode(fn, msg, obs_dim, act_dim, with_baseline, cap):
     L = _lib.lib()
     cap = cap if cap is not None else len(msg) // 2 + 1
     cols = {"obs": np.empty((cap, obs_dim), np.float32), "act": np.empty(cap, np.float32),
             "mask": np.empty((cap, act_dim), np.float32), "rew": np.empty(cap, np.float32),
             "val": np.empty(cap, np.float32), "logp": np.empty(cap, np.float32), "done": np.empty(cap, np.uint8)}
     n, err = C.c_int64(), C.create_string_buffer(256)
-    st = L.rrl_decode_grpc_trajectory(msg, len(msg), obs_dim, act_dim, int(bool(with_baseline)), _ptr(cols["obs"]),
+    st = fn(msg, len(msg), obs_dim, act_dim, int(bool(with_baseline)), _ptr(cols["obs"]),
                                       _ptr(cols["act"]), _ptr(cols["mask"]), _ptr(cols["rew"]), _ptr(cols["val"]),
                                       _ptr(cols["logp"]), _ptr(cols["done"]), cap, C.byref(n), err, len(err))
     if st != _lib.RRL_OK:

@@ -348,3 +348,42 @@ def test_tc_gradients_many_tiles_vs_float64_autograd(n, d, A):
         np.testing.assert_allclose(g, want, rtol=1e-5, atol=max(2.0 * e_ref, 3e-6 * np.abs(want).max()), err_msg=gkey)
         np.testing.assert_allclose(loss, float(ref[lkey]), rtol=1e-5, atol=1e-7, err_msg=lkey)
     L.close()
+
+
+def test_pickle_ingest_matches_golden_epoch_and_is_all_or_nothing():
+    """rrl_ingest_pickle: the golden epoch's inputs sent as ZMQ trajectory messages (one pickled Vec<RelayRLAction> per
+    episode, terminal marker last: src/types/trajectory.rs:183-193) give the reference's offsets, returns and
+    advantages; a message with a bad action in the middle leaves the buffer exactly as it was."""
+    import pickle
+    from test_wire_pickle import _graph
+    import pipe_driver as pd
+    from relayrl_b200 import RelayRLB200Error
+    g = load_golden("epoch_vf_h128")
+    L, d, A, H, wb = _mk(g, iters=1)
+    p = "e0_"
+    acts, sent, n_in = [], 0, len(g[p + "in_done"])
+    for i in range(n_in):
+        if g[p + "in_done"][i]:
+            acts.append(pd.rf.RelayRLAction(None, None, None, float(g[p + "in_rew"][i]), None, True, False))
+            if sent == 0:   # first message: also try a corrupted copy -- nothing of it may stay in the buffer
+                bad = _graph(acts)
+                bad[len(bad) // 2]["mask"]["data"] = bad[len(bad) // 2]["mask"]["data"][:-3]
+                with pytest.raises(RelayRLB200Error) as e:
+                    L.ingest_pickle(pickle.dumps(bad, protocol=3))
+                assert e.value.status == -6
+                assert np.array_equal(L.offsets(), [0])
+            sent += L.ingest_pickle(pickle.dumps(_graph(acts, bytes_as="bytes" if sent % 2 else "list"), protocol=3))
+            acts = []
+        else:
+            acts.append(pd.rf.RelayRLAction(np.asarray(g[p + "in_obs"][i], np.float64), np.array([g[p + "in_act"][i]], np.float32),
+                                            np.asarray(g[p + "in_mask"][i], np.float64), float(g[p + "in_rew"][i]),
+                                            {"logp_a": np.array([g[p + "in_logp"][i]], np.float32),
+                                             "v": np.array(g[p + "in_val"][i], np.float32)}, False, False))
+    if acts:
+        sent += L.ingest_pickle(pickle.dumps(_graph(acts), protocol=3))
+    assert sent == n_in
+    n, _ = L.finish()
+    assert np.array_equal(L.offsets(), g[p + "offsets"])
+    np.testing.assert_allclose(L.returns(n), g[p + "ret_raw"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(L.advantages(n, normalised=False), g[p + "adv_raw"], rtol=1e-6, atol=1e-6)
+    L.close()

@@ -8,9 +8,12 @@ library (which caps the size at RRL_SCAN_NOALLOC_MAX transitions).
 
 The test drives the entry point through the C ABI twice in a row -- with different sizes and both
 baseline modes, so the second call runs over whatever the first one left in the shared scratch --
-and compares every output with the ordinary entry point (rrl_scan_device + caller workspace) at
-the tolerance of tests/test_gpu_scan.py.  It lives in a file that sorts last so that a run
-stopping at the first failure has already executed every other test.
+and compares every output with the ordinary entry point (rrl_scan_device + caller workspace) AND
+with the CPU oracle (oracle/scan_ref.c, the sequential float64 recurrence) at the tolerance of
+tests/test_gpu_scan.py.  The second call goes out on a stream of the caller's own.  Around each
+call the free device memory reported by the driver must not move: the point of the entry point is
+that it allocates nothing.  It lives in a file that sorts last so that a run stopping at the first
+failure has already executed every other test.
 """
 import ctypes as C
 
@@ -41,14 +44,24 @@ def _case(rng, n, dev):
 def test_noalloc_matches_workspace_entry_point_twice():
     import torch
     from relayrl_b200 import _lib, scan_workspace_bytes
+    from oracle import scan_ref as sr
     L = _lib.lib()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     rng = np.random.default_rng(2024)
     g, l = float(np.float32(0.98)), float(np.float32(0.97))
     p = lambda t: C.c_void_p(t.data_ptr())
-    # two consecutive calls: a large with-baseline batch, then a smaller without-baseline one
-    for n, wb in ((3_000_001, 1), (777_777, 0)):
+    own_stream = torch.cuda.Stream(device=dev)
+    # The first call on a device is the documented set-up call (it resolves the scratch array's device address, and with
+    # CUDA's lazy module loading the driver may bring the kernel image in at that moment): make it a tiny one, outside
+    # the free-memory bracket.
+    z, zo = torch.zeros(16, device=dev), torch.tensor([0, 16], dtype=torch.int64, device=dev)
+    assert L.rrl_scan_device_noalloc(p(z), p(z), p(zo), p(z), 16, 1, g, l, 1, p(z.clone()), p(z.clone()), None, None) == 0
+    assert L.rrl_scan_device_noalloc(p(z), p(z), p(zo), p(z), 16, 1, g, l, 0, p(z.clone()), p(z.clone()), None, None) == 0
+    torch.cuda.synchronize()
+    # two consecutive calls: a large with-baseline batch on the default stream, then a smaller without-baseline one on
+    # the caller's own stream
+    for (n, wb), stream in zip(((3_000_001, 1), (777_777, 0)), (None, own_stream)):
         d, E = _case(rng, n, dev)
         outs = []
         for which in ("noalloc", "workspace"):
@@ -56,8 +69,13 @@ def test_noalloc_matches_workspace_entry_point_twice():
             stats = torch.zeros(8, dtype=torch.float64, device=dev)
             torch.cuda.synchronize()
             if which == "noalloc":
+                free0, _ = torch.cuda.mem_get_info(dev)
                 st = L.rrl_scan_device_noalloc(p(d["rew"]), p(d["val"]), p(d["offs"]), p(d["lvs"]), n, E, g, l, wb,
-                                               p(adv), p(ret), p(stats), None)
+                                               p(adv), p(ret), p(stats),
+                                               C.c_void_p(stream.cuda_stream) if stream is not None else None)
+                torch.cuda.synchronize()
+                free1, _ = torch.cuda.mem_get_info(dev)
+                assert free1 == free0, "the no-allocation entry point changed free device memory: %d -> %d" % (free0, free1)
             else:
                 ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
                 st = L.rrl_scan_device(p(d["rew"]), p(d["val"]), p(d["offs"]), p(d["lvs"]), n, E, g, l, wb, p(adv),
@@ -72,6 +90,12 @@ def test_noalloc_matches_workspace_entry_point_twice():
         np.testing.assert_allclose(s0[:2], s1[:2], rtol=1e-9)          # sum, sum of squares (f64)
         np.testing.assert_allclose(s0[3:5], s1[3:5], rtol=1e-6, atol=1e-7)   # mean, std (f32 values)
         assert np.abs(a0).max() > 0 and np.isfinite(a0).all() and np.isfinite(r0).all()
+        # the checker of record: the sequential float64 recurrence on the host
+        a_ref, r_ref = sr.finish_paths(d["rew"].cpu().numpy(), d["val"].cpu().numpy(), d["offs"].cpu().numpy(),
+                                       d["lvs"].cpu().numpy(), g, l, bool(wb))
+        np.testing.assert_allclose(a0, a_ref, rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(r0, r_ref, rtol=RTOL, atol=ATOL)
+        assert np.mean(a0 != a_ref) < 1e-3
 
 
 def test_noalloc_rejects_sizes_beyond_the_static_scratch():
