@@ -130,46 +130,80 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-def cpu_baseline(sample_n, iters, threads, seed=7):
+def cpu_baseline(sample_n, iters, threads, seed=7, store_prefix=0):
     """The oracle port of the reference CPU learner (oracle/learner_oracle.py) on a bounded sample of
-    the same workload: ingest (segment + store) -> finish_path per episode -> get() -> train_model."""
+    the same workload: ingest (segment + store) -> finish_path per episode -> get() -> train_model.
+    Returns (transitions/s, seconds, stage split).  The port's ingest is VECTORISED (one numpy gather per column) where
+    the reference loops per transition in Python (REINFORCE.py:72-87): that is generous to the CPU; with store_prefix
+    > 0 the reference-style loop (oracle.store_loop) is timed on that many actions beside it."""
     import torch
     from oracle import learner_oracle as lo
     torch.set_num_threads(threads)
     st = make_stream(sample_n, seed, pinned=False)
     O = lo.OracleLearner(D, A, sample_n + 1, hidden=H, with_baseline=True, gamma=GAMMA, lam=LAM,
                          train_vf_iters=iters, seed=1)
+    cols = [st[k].numpy() for k in ("obs", "act", "mask", "rew", "val", "logp", "done")]
     t0 = time.perf_counter()
-    O.ingest(st["obs"].numpy(), st["act"].numpy(), st["mask"].numpy(), st["rew"].numpy(), st["val"].numpy(),
-             st["logp"].numpy(), st["done"].numpy())
-    O.train()
-    dt = time.perf_counter() - t0
-    return sample_n / dt, dt
+    O.ingest(*cols)
+    t1 = time.perf_counter()
+    data, _ = O.get()
+    t2 = time.perf_counter()
+    out = lo.train_epoch(O.pi, O.v, data, O.pi_lr, O.vf_lr, O.iters)
+    t3 = time.perf_counter()
+    split = {"ingest_vectorised_s": t1 - t0, "get_s": t2 - t1, "train_model_s": t3 - t2,
+             "transitions_per_s_without_ingest": sample_n / (t3 - t1)}
+    if store_prefix:
+        k = min(store_prefix, st["rows"])
+        t4 = time.perf_counter()
+        lo.store_loop(*[c[:k] for c in cols], lo_f32(GAMMA), lo_f32(LAM), True)
+        split["reference_style_store_loop"] = {"actions": int(k), "actions_per_s": k / (time.perf_counter() - t4)}
+    dt = t3 - t0
+    return sample_n / dt, dt, split
+
+
+def lo_f32(x):
+    return float(np.float32(x))
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU learner (oracle port; the reference is Python and
-    cannot travel to the GPU box) on the host cores, bounded sample per step."""
+    """--impl reference: the reference's CPU learner (oracle port; the reference is Python + Rust and cannot travel to
+    the GPU box) on the host cores.  Each timed step is one full epoch on a BOUNDED SAMPLE of the workload
+    (--ref-sample transitions, not the GPU arm's 64 Mi): `config` says so and `extrapolated_to` names the size the
+    GPU arm runs.  After the timed steps the epoch is run once at each --ref-linearity size: the per-transition cost is
+    flat to slightly rising with N, so the sample does not flatter the GPU."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     sample = args.ref_sample
-    times = []
+    times, split = [], None
     for i in range(args.warmup + args.steps):
-        tps, dt = cpu_baseline(sample, ITERS, threads, seed=7 + i)
+        tps, dt, sp = cpu_baseline(sample, ITERS, threads, seed=7 + i,
+                                   store_prefix=(1 << 20) if i == args.warmup + args.steps - 1 else 0)
         if i >= args.warmup:
             times.append(dt)
+            split = sp
     ms = 1000.0 * sum(times) / len(times)
     value = sample / (ms / 1000.0)
+    linearity = [{"transitions": sample, "transitions_per_s": value, "us_per_transition": 1e6 / value}]
+    for n in args.ref_linearity:
+        if n > 0:
+            tps, dt, _ = cpu_baseline(n, ITERS, threads, seed=99)
+            linearity.append({"transitions": n, "transitions_per_s": tps, "us_per_transition": 1e6 / tps})
     sample_desc = "%d transitions (C3 length mixture), full epoch with %d value iterations, per step" % (sample, ITERS)
+    cfg = workload_config(args, sample)
+    cfg["sampled"] = True
+    cfg["extrapolated_to"] = args.n
+    cfg["note"] = "CPU arm timed on a bounded sample of the GPU arm's workload; per-transition cost vs size in `linearity`"
     print(json.dumps({
         "impl": "reference", "metric": "learner transitions/sec", "value": value, "unit": "transitions/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, args.n),   # the GPU arm's workload; each step times a bounded sample of it
+        "config": cfg,
         "cpu_baseline": {"value": value, "unit": "transitions/s", "cores": threads, "kind": "port",
-                         "sample": sample_desc},
+                         "sample": sample_desc, "stages": split, "linearity": linearity,
+                         "ingest_note": "the port's ingest is vectorised; the reference's per-transition store loop is "
+                                        "timed separately (stages.reference_style_store_loop)"},
         "e2e": {"value": value, "unit": "transitions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -322,6 +356,98 @@ def measure_without_baseline(dev, local, n=1 << 20, reps=5):
             "cpu_transitions_per_s": n / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
 
 
+def correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world):
+    """Outside every timed region: the result of the path the bench just timed, checked on the spot.
+    (1) value and policy loss and the value gradient at the CURRENT weights, from the library (rrl_eval_grad: the same
+        kernels as a training step, gradient all-reduced over the ranks) against a float64 evaluation of the same device
+        buffers by plain torch (tests/f64_eval.py; sums all-reduced over the ranks): rel 1e-5 on the losses, 3e-5 in the
+        L2 norm on the gradient (tests/test_gpu_scale.py explains the bound);
+    (2) at N > 1: every rank holds bit-identical weights after the timed steps (same all-reduced float64 gradient, same
+        Adam) -- the data-parallel replicas never need a broadcast.
+    A failure raises: a SCALE run that diverged does not print a line."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import f64_eval
+    pi, vf = L.get_params(0), L.get_params(1)
+    out = {}
+    if world > 1:
+        mine = torch.from_numpy(np.concatenate([pi, vf])).to(dev)
+        ref = mine.clone()
+        dist.broadcast(ref, 0)
+        same = torch.tensor([int(torch.equal(mine, ref))], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        out["replicas_bit_identical"] = bool(same.item())
+        assert out["replicas_bit_identical"], "data-parallel replicas hold different weights"
+    L.ingest_device(cols["obs"], cols["act"], cols["mask"], cols["rew"], cols["val"], cols["logp"], n, offsets, last_vals)
+    L.finish()
+    adv = torch.from_numpy(L.advantages(n, True).copy()).to(dev)
+    ret = torch.from_numpy(L.returns(n).copy()).to(dev)
+    gp, lp = L.eval_grad(0)
+    gv, lv = L.eval_grad(1)
+    L.reset_buffer()
+    got = torch.tensor([lp[0], lv[0]], dtype=torch.float64, device=dev)   # this rank's sums over the global N
+    r = f64_eval.evaluate(pi, vf, D, H, A, cols, adv, ret, n_global=n * world, dtype=torch.float64)
+    want = torch.tensor([r["loss_pi"], r["loss_v"]], dtype=torch.float64, device=dev)
+    g64 = torch.from_numpy(r["v_grad"]).to(dev)
+    if world > 1:
+        dist.all_reduce(got), dist.all_reduce(want), dist.all_reduce(g64)
+    got, want = got.tolist(), want.tolist()
+    g64 = g64.cpu().numpy()
+    out.update(loss_v=got[1], loss_v_float64=want[1], loss_pi=got[0], loss_pi_float64=want[0],
+               value_grad_rel_l2=float(np.linalg.norm(gv - g64) / np.linalg.norm(g64)))
+    assert abs(got[1] - want[1]) <= 1e-5 * abs(want[1]), out
+    assert abs(got[0] - want[0]) <= 1e-5 * abs(want[0]) + 1e-7, out
+    assert out["value_grad_rel_l2"] <= 3e-5, out
+    out["passed"] = True
+    return out
+
+
+def measure_c1(dev, local, hidden, epochs=20):
+    """C1: CartPole-shaped epochs -- 8 trajectories of U{8..500} transitions, f64 obs/mask on the
+    wire, with baseline, 80 value iterations -- through rrl_ingest_packed + rrl_train_epoch (the calls the plug-in
+    makes): latency per epoch, host wall clock around the calls (the regime is launch/latency-bound, not bandwidth-
+    bound).  Beside it the oracle port on the host cores, same epochs."""
+    import torch
+    from relayrl_b200 import Learner
+    rng = np.random.default_rng(1)
+    L = Learner(D, A, 8 * 500 + 8, hidden=hidden, with_baseline=True, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS, device=local)
+    L.set_params(0, linear_init(D, hidden, A, 1)[1])
+    L.set_params(1, linear_init(D, hidden, 1, 2)[1])
+    eps = []
+    for _ in range(epochs + 3):
+        lens = rng.integers(8, 501, 8)
+        done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
+        n = len(done)
+        eps.append((rng.standard_normal((n, D)), rng.integers(0, A, n).astype(np.float32), np.ones((n, A)),
+                    np.ones(n, np.float32), rng.standard_normal(n).astype(np.float32),
+                    rng.standard_normal(n).astype(np.float32), done))
+    times, launches = [], 0
+    for i, e in enumerate(eps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        L.ingest(*e)
+        st = L.train_epoch()          # returns after the stream has drained (stats come back to the host)
+        if i >= 3:
+            times.append(time.perf_counter() - t0)
+            launches = st["kernel_launches"]
+    L.close()
+    from oracle import learner_oracle as lo
+    torch.set_num_threads(os.cpu_count() or 1)
+    O = lo.OracleLearner(D, A, 8 * 500 + 8, hidden=hidden, with_baseline=True, gamma=GAMMA, lam=LAM, train_vf_iters=ITERS, seed=1)
+    ctimes = []
+    for i, e in enumerate(eps[:6]):
+        t0 = time.perf_counter()
+        O.ingest(*e)
+        O.train()
+        if i >= 1:
+            ctimes.append(time.perf_counter() - t0)
+    ms, cms = 1e3 * sorted(times)[len(times) // 2], 1e3 * sorted(ctimes)[len(ctimes) // 2]
+    mean_n = float(np.mean([int((e[6] == 0).sum()) for e in eps]))
+    return {"workload": "C1: 8 trajectories per epoch (%.0f transitions on average), d=4 A=2 H=%d, with baseline, 80 value iterations" % (mean_n, hidden),
+            "ms_per_epoch": ms, "kernel_launches_per_epoch": launches, "transitions_per_s": mean_n / (ms * 1e-3),
+            "cpu_ms_per_epoch": cms, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
+
+
 def run_scan_only(args):
     import torch
     dev = torch.device("cuda", 0)
@@ -415,8 +541,9 @@ def run_ours(args):
         sampler.start()
     dt, stats = timed(step_device, args.steps, args.warmup)
     clocks = sampler.finish() if rank == 0 else None
-    dt_e2e, stats_e2e = timed(step_e2e, max(1, min(args.steps, 2)), 1)
-    e2e_steps = max(1, min(args.steps, 2))
+    dt_e2e, stats_e2e = timed(step_e2e, args.steps, 1)   # the same number of timed steps as `value`
+    e2e_steps = args.steps
+    check = None if args.no_check else correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world)
 
     scan_ms = measure_scan(cols, offsets, last_vals, n, dev)
     extras = {}
@@ -429,6 +556,7 @@ def run_ours(args):
                                         "bytes_per_transition": 8}
         extras["actor"] = measure_actor(dev)
         extras["without_baseline"] = measure_without_baseline(dev, local)
+        extras["c1"] = [measure_c1(dev, local, 64), measure_c1(dev, local, 128)]
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -445,7 +573,9 @@ def run_ours(args):
     achieved_tf = flops_per_launch / (value_launch_ms * 1e-3) / 1e12
     scan_gbs = 16.0 * n / (scan_ms * 1e-3) / 1e9
     cpu_threads = os.cpu_count() or 1
-    cpu_tps, cpu_dt = cpu_baseline(args.cpu_sample, ITERS, cpu_threads)
+    # the reported baseline is taken on rank 0 at N = 1 only (with N ranks on one host the oracles would fight for the
+    # cores); the driver's separate --impl reference run is the comparable figure at every N
+    cpu_tps, cpu_dt, cpu_split = cpu_baseline(args.cpu_sample, ITERS, cpu_threads) if world == 1 else (None, 0.0, None)
     line = {
         "metric": "learner transitions/sec", "value": value, "unit": "transitions/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
@@ -472,8 +602,10 @@ def run_ours(args):
                           "bytes_per_transition": 16, "launch_ms": scan_ms},
         "stage_ms": {"scan": s["ms_scan"], "policy": s["ms_policy"], "value": s["ms_value"]},
         "cpu_baseline": {"value": cpu_tps, "unit": "transitions/s", "cores": cpu_threads, "kind": "port",
-                         "sample": "%d transitions, full epoch with %d value iterations, %.1f s" % (args.cpu_sample, ITERS, cpu_dt)},
+                         "sample": "%d transitions, full epoch with %d value iterations, %.1f s" % (args.cpu_sample, ITERS, cpu_dt),
+                         "stages": cpu_split} if world == 1 else None,
         "losses": {"loss_pi": s["loss_pi"], "loss_v": s["loss_v"], "entropy": s["entropy"]},
+        "check": check,
     }
     if "roofline_normalise" in extras:
         extras["roofline_normalise"].update(peak=hbm, frac=extras["roofline_normalise"]["achieved"] / hbm, peak_source=which)
@@ -492,6 +624,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=1 << 17)
     ap.add_argument("--ref-sample", type=int, default=1 << 17)
+    ap.add_argument("--ref-linearity", type=int, nargs="*", default=[1 << 20, 1 << 22],
+                    help="sizes at which the CPU arm runs one more epoch each (per-transition cost vs N)")
+    ap.add_argument("--no-check", action="store_true", help="skip the float64 correctness check after the timed steps")
     ap.add_argument("--no-extras", action="store_true", help="skip the K3 and actor (C4) side measurements")
     ap.add_argument("--scan-only", action="store_true", help="measure K2 alone (roofline_scan) and exit")
     args = ap.parse_args()

@@ -46,6 +46,42 @@ def segment(done: np.ndarray, rew: np.ndarray, start_ptr: int = 0):
     return keep, offsets, last_vals
 
 
+def store_loop(obs, act, mask, rew, val, logp, done, gamma, lam, with_baseline):
+    """The reference's ingest exactly as it runs: one Python iteration per action
+    (REINFORCE.receive_trajectory, REINFORCE.py:72-87), ReplayBuffer.store per transition
+    (replay_buffer.py:34-46: six element-wise assignments into f32 numpy buffers) and finish_path -- two lfilter
+    calls -- at every terminal marker (replay_buffer.py:48-79).  Used as the timed CPU baseline of the ingest stage
+    (BASELINE.md section 3); OracleLearner.ingest is the vectorised form of the same thing and far kinder to the CPU.
+    Returns (ptr, adv_buf, ret_buf)."""
+    n = len(done)
+    d, A = obs.shape[1], mask.shape[1]
+    obs_buf, mask_buf = np.zeros((n, d), np.float32), np.zeros((n, A), np.float32)
+    act_buf, rew_buf, val_buf, logp_buf, adv_buf, ret_buf = (np.zeros(n, np.float32) for _ in range(6))
+    ptr = path_start = 0
+    for i in range(n):
+        if done[i]:
+            lv = float(rew[i])
+            sl = slice(path_start, ptr)
+            if with_baseline:
+                rews, vals = np.append(rew_buf[sl], lv), np.append(val_buf[sl], lv)
+                deltas = rews[:-1] + gamma * vals[1:] - vals[:-1]
+                adv_buf[sl] = discount_cumsum(deltas, gamma * lam)
+                ret_buf[sl] = discount_cumsum(rews, gamma)[:-1]
+            else:
+                adv_buf[sl] = discount_cumsum(rew_buf[sl], gamma * lam)
+                ret_buf[sl] = discount_cumsum(rew_buf[sl], gamma)
+            path_start = ptr
+        else:
+            obs_buf[ptr] = obs[i]
+            act_buf[ptr] = act[i]
+            mask_buf[ptr] = mask[i]
+            rew_buf[ptr] = rew[i]
+            val_buf[ptr] = val[i] if with_baseline else 0.0
+            logp_buf[ptr] = logp[i]
+            ptr += 1
+    return ptr, adv_buf, ret_buf
+
+
 # --------------------------------------------------------------------------------------
 # a2: discounted reverse scan            (_common/_algorithms/BaseReplayBuffer.py:12-27,
 #                                          algorithms/REINFORCE/replay_buffer.py:48-79)

@@ -267,8 +267,11 @@ def build_module(obs_dim, act_dim, hidden, with_baseline):
             with torch.no_grad():
                 probs, logits = self.policy(obs, mask)
                 act = torch.multinomial(probs, 1)
-                # per-env raw masked logit; batch 1 gives shape [1] like the reference
-                logp_a = logits.gather(-1, act).squeeze(-1)
+                # raw masked logit of the sampled action, with the reference's shapes
+                # (kernel.py:33-37: the 1-D obs agents send gives [1], a [1, d] batch gives [1, 1])
+                a = act.long().unsqueeze(-1)
+                a, lp = torch.broadcast_tensors(a, logits)
+                logp_a = lp.gather(-1, a[..., :1]).squeeze(-1)
                 data = {"logp_a": logp_a}
                 if self.has_v:
                     data["v"] = self.baseline(obs)

@@ -14,7 +14,7 @@
 // episode end resets the carry.  Because c is a constant, the slope of any run of whole threads / warps / tiles
 // is a constant power of c (or 0 when a path ends inside it): only VALUES travel through shuffles, shared
 // memory and the tile descriptors.  One pass over HBM (16 B/transition with baseline, 12 B without):
-//   persistent CTAs taking 2048-transition tiles from a ticket counter, right-most first; a producer warp
+//   persistent co-resident CTAs walking 2048-transition tiles right-to-left in a fixed stride; a producer warp
 //   prefetches the next tile while 8 consumer warps scan the current one
 //     -> cp.async 16-byte copies into swizzled shared memory, blocked 8-per-thread reads
 //     -> episode ends of the tile found by a 32-ary warp search in `offsets`
@@ -95,9 +95,7 @@ struct ScanArgs {
 };
 
 // ---- persistent, warp-specialised tile pipeline ------------------------------------------------
-// A CTA is 8 consumer warps + 1 producer warp and takes tiles from a ticket counter, right-most tile first, so every
-// tile a look-back can wait for has already been claimed by a CTA that is running: no co-residency requirement, no
-// cooperative launch, and the CTAs of an SM drift apart instead of hitting their barriers in lock-step.
+// A CTA is 8 consumer warps + 1 producer warp.
 // While the consumers work on one tile the producer warp prepares the next one in the other buffer: cp.async of
 // rew/val into swizzled shared memory (the bytes in flight that keep HBM busy), the 32-ary search for the tile's
 // first path boundary, and the end-of-path bit mask + last_vals.
@@ -120,6 +118,20 @@ struct ScanCtl {  // consumer hand-offs inside one tile
 };
 constexpr double SCAN_CUT = 1e-100;
 
+#ifdef SCAN_TIMING  // developer build only: clock64 spans of CTA 0 (warp 1 of the consumers, lane 0; the producer's lane 0)
+__device__ unsigned long long g_scan_timing[16];
+#define SCT_DECL long long sct_prev = clock64()
+#define SCT(slot, cond)                                                                          \
+    do {                                                                                         \
+        const long long sct_now = clock64();                                                     \
+        if (blockIdx.x == 0 && (cond)) atomicAdd(&g_scan_timing[slot], (unsigned long long)(sct_now - sct_prev)); \
+        sct_prev = sct_now;                                                                      \
+    } while (0)
+#else
+#define SCT_DECL
+#define SCT(slot, cond)
+#endif
+
 __device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gmem_src, int src_bytes)
 {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -129,11 +141,10 @@ __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;"
 
 // producer warp: claim the next tile and fill `B` for it (or mark it empty)
 template <bool WB>
-__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int64_t n_scan, int num_tiles, int lane)
+__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int64_t n_scan, int num_tiles, int lane, int j)
 {
-    int j = 0;
-    if (lane == 0) j = atomicAdd(a.ticket, 1) + 1;  // logical tile: 0 is the right-most
-    j = __shfl_sync(0xffffffffu, j, 0);
+    // j: logical tile, 0 is the right-most
+    SCT_DECL;
     const int tile = j < num_tiles ? num_tiles - 1 - j : -1;
     if (lane == 0) B.tile = tile;
     if (tile < 0) return;
@@ -149,6 +160,7 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
         if (WB) cp_async16_zfill(&B.v[sidx(4 * c)], a.val + g, valid);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
+    SCT(8, lane == 0);  // producer: issue
     if (WB && lane == 0) B.v[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
 
 #ifdef SCAN_DBG_NO_SEARCH  // timing experiment only (wrong results)
@@ -193,7 +205,9 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
         }
         if (!__any_sync(0xffffffffu, more)) break;  // offsets are sorted: nothing further can fall in the tile
     }
+    SCT(9, lane == 0);  // producer: search + mask
     asm volatile("cp.async.wait_all;" ::: "memory");
+    SCT(10, lane == 0);  // producer: wait for the data
 }
 
 // consumer warps (threads 0..255): scan the tile in `B`, publish / look back, write the outputs.
@@ -203,6 +217,8 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                                              ScanCtl &S, int tid, double lane_r, double lane_a, int parity)
 {
     const int lane = tid & 31, warp = tid >> 5;
+    SCT_DECL;
+    const bool sct_me = tid == 32;
     const float *r_s = B.r, *v_s = B.v;
     const int64_t t0 = (int64_t)tile * SCAN_TILE;
     const int cnt = (int)min((int64_t)SCAN_TILE, n_scan - t0);
@@ -270,6 +286,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
     }
 
+    SCT(0, sct_me);  // loads + pass 1
     // ---- warp suffix scan: sr/sa = value at this lane's first element for a zero carry into the warp ----------
     // A step over d lanes multiplies by c^(8d) unless a path ends among the d lanes it bridges: the slope of an open
     // run of whole threads is a constant, so only the two values travel (two 64-bit shuffles per step).
@@ -286,7 +303,9 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
     if (lane == 31) er = 0.0, ea = 0.0;
     const bool lane_open = (above >> 1) == 0u;  // no path ends to the right of this lane inside the warp
     if (lane == 0) S.wagg[warp] = make_double2(sr, sa), S.wclosed[warp] = em;
+    SCT(1, sct_me);  // warp scan
     consumer_sync();
+    SCT(2, sct_me);  // barrier 1
 
     // ---- warp 0: the eight warps, the tile's descriptor, the look-back -------------------------------------
     if (warp == 0) {
@@ -371,6 +390,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
     }
     consumer_sync();
+    SCT(3, sct_me);  // warp 0's combine + look-back (as seen by a waiting warp)
 
     // ---- pass 2: add the carry, round to f32, statistics, stores straight from registers -------------------------
     double s1 = 0.0, s2 = 0.0;
@@ -422,6 +442,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         s2 += __shfl_xor_sync(0xffffffffu, s2, d);
     }
     if (lane == 0) S.wstat[parity][warp] = make_double2(s1, s2);
+    SCT(4, sct_me);  // pass 2 + stores + statistics
 }
 
 template <bool WB>
@@ -445,7 +466,14 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
         for (int i = 0; i < lane; ++i) tr *= a.tp_r, ta *= a.tp_a;
         ctl.tpow[lane] = make_double2(tr, ta);
     }
-    if (producer) scan_prepare<WB>(a, buf[0], n_scan, num_tiles, lane);
+    // CTA c owns the logical tiles c, c + G, c + 2G, ...: the launch is cooperative (all G CTAs co-resident), the CTAs
+    // move through their tiles in step, and with the look-back cut-off a tile only ever waits for the few tiles next to
+    // it, which the neighbouring CTAs publish at the same moment.  (Tiles handed out by a ticket counter were tried:
+    // the producer has to claim a tile one step before its CTA starts it, and that skew made the look-back wait
+    // erratically -- 0.6 to 3.6 ms for the same input.)
+    const int G = gridDim.x;
+    int j = blockIdx.x;
+    if (producer) scan_prepare<WB>(a, buf[0], n_scan, num_tiles, lane, j);
     __syncthreads();
     int b = 0, prev_tile = -1;
     while (true) {
@@ -458,11 +486,19 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
             a.partials[prev_tile] = make_double2(t1, t2);
         }
         if (tile < 0) break;
+        j += G;
         if (producer)
-            scan_prepare<WB>(a, buf[b ^ 1], n_scan, num_tiles, lane);
+            scan_prepare<WB>(a, buf[b ^ 1], n_scan, num_tiles, lane, j);
         else
             scan_consume<WB>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b);
+        SCT_DECL;
         __syncthreads();
+        SCT(5, tid == 32);                // consumers waiting for the producer
+        SCT(11, tid == SCAN_THREADS);     // producer waiting for the consumers
+        SCT(12, tid == 32);               // (tile count: every span adds ~0, used as a divisor via slot 13)
+#ifdef SCAN_TIMING
+        if (blockIdx.x == 0 && tid == 32) atomicAdd(&g_scan_timing[13], 1ull);
+#endif
         prev_tile = tile;
         b ^= 1;
     }
@@ -584,6 +620,18 @@ WsLayout ws_layout(int64_t n)
 
 }  // namespace
 
+#ifdef SCAN_TIMING
+extern "C" int32_t rrl_debug_scan_timing(unsigned long long *out16, int32_t reset)
+{
+    if (out16 && cudaMemcpyFromSymbol(out16, g_scan_timing, sizeof(g_scan_timing)) != cudaSuccess) return RRL_ECUDA;
+    if (reset) {
+        unsigned long long z[16] = {};
+        if (cudaMemcpyToSymbol(g_scan_timing, z, sizeof(z)) != cudaSuccess) return RRL_ECUDA;
+    }
+    return RRL_OK;
+}
+#endif
+
 size_t scan_workspace_bytes(int64_t n) { return ws_layout(n).total; }
 
 int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, const float *last_vals,
@@ -657,13 +705,12 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
             }
             sms_cached = sms, per_sm_cached[which] = per_sm;
         }
-        // persistent CTAs, as many as fit; tiles come from the ticket counter, so nothing depends on co-residency
+        // co-resident by construction: the look-back spins on tiles owned by other CTAs
         const int grid = std::min(tiles, per_sm_cached[which] * sms_cached);
-        if (with_baseline)
-            scan_kernel<true><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a);
-        else
-            scan_kernel<false><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a);
-        RRL_CUDA_OK(cudaGetLastError(), err);
+        const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
+                                       : reinterpret_cast<const void *>(scan_kernel<false>);
+        void *args[] = {&a};
+        RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SCAN_CTA_THREADS), args, smem, stream), err);
         if (launches) *launches += 1;
     }
     if (stats_out) {

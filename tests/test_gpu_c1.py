@@ -1,0 +1,122 @@
+"""Config C1 (BASELINE.json configs[0]): REINFORCE with baseline on CartPole-shaped data,
+d = 4, A = 2, 8 trajectories per epoch, 50 epochs -- (a) the CUDA learner against the oracle EVERY epoch, at H = 64 (the
+config's 2x64 MLP) and H = 128 (the reference's hard-coded size, Q8); (b) the drop-in plug-in REINFORCE_B200 driven over a
+pipe by the worker (the unmodified python_algorithm_reply.py where the reference tree exists, else its restatement
+tests/worker_standin.py -- tests/test_worker_pipe.py pins the two against each other), with the stand-in for the PyO3
+module, JSON lines in, {"status": ...} lines out, TorchScript hand-off after every epoch.
+
+Per-epoch parity is teacher-forced: before each epoch the oracle is given the CUDA learner's weights and Adam state, so
+every epoch is judged on its own (81 Adam steps from identical state) instead of on 50 epochs of compounding 1e-7s.
+The free-running distance after 50 epochs is printed."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import pipe_driver as pd
+from oracle import learner_oracle as lo
+from test_gpu_learner import assert_weights_close
+
+pytestmark = pytest.mark.gpu
+
+
+def _torch_adam(params, lr, m, v, step):
+    """torch.optim.Adam holding the given moments (what REINFORCE.py:47,50 would hold at this point)."""
+    opt = torch.optim.Adam(params, lr=lr)
+    o = 0
+    for p in params:
+        k = p.numel()
+        opt.state[p] = {"step": torch.tensor(float(step)), "exp_avg": torch.from_numpy(m[o:o + k].copy()).reshape(p.shape),
+                        "exp_avg_sq": torch.from_numpy(v[o:o + k].copy()).reshape(p.shape)}
+        o += k
+    return opt
+
+
+@pytest.mark.parametrize("H", [64, 128])
+def test_c1_fifty_epochs_against_the_oracle(H):
+    from relayrl_b200 import Learner
+    d, A, epochs, iters = 4, 2, 50, 80
+    rng = np.random.default_rng(1)
+    L = Learner(d, A, 8 * 500 + 8, hidden=H, with_baseline=True, train_vf_iters=iters)
+    pi0, v0 = lo.init_params(d, H, A, 1), lo.init_params(d, H, 1, 2)
+    L.set_params(0, lo.flatten(pi0).numpy()), L.set_params(1, lo.flatten(v0).numpy())
+    free = lo.OracleLearner(d, A, 8 * 500 + 8, hidden=H, with_baseline=True, train_vf_iters=iters, seed=1)
+    free.pi, free.v = [p.clone().requires_grad_(True) for p in pi0], [p.clone().requires_grad_(True) for p in v0]
+    seen = [set(), set()]
+    for ep in range(epochs):
+        def policy(obs):   # actions, logp_a, v as the oracle model's step would report them (kernel.py:99-107)
+            with torch.no_grad():
+                o = torch.from_numpy(obs)
+                act, out = lo.actor_step(lo.unflatten(L.get_params(0), d, H, A), lo.unflatten(L.get_params(1), d, H, 1), o,
+                                         torch.ones(len(obs), A))
+            return act.reshape(-1).numpy(), out["logp_a"].numpy(), out["v"].numpy()
+        acts = []
+        for _ in range(8):
+            acts += pd.c1_trajectory(rng, policy=policy)
+        cols = pd.actions_to_columns(acts, d, A)
+        # teacher forcing: the oracle starts this epoch from the CUDA learner's state
+        O = lo.OracleLearner(d, A, 8 * 500 + 8, hidden=H, with_baseline=True, train_vf_iters=iters, seed=1)
+        O.pi = [p.requires_grad_(True) for p in lo.unflatten(L.get_params(0), d, H, A)]
+        O.v = [p.requires_grad_(True) for p in lo.unflatten(L.get_params(1), d, H, 1)]
+        (mp, vp, sp), (mv, vv, sv) = L.get_opt_state(0), L.get_opt_state(1)
+        if sp:
+            O._pi_opt, O._v_opt = _torch_adam(O.pi, O.pi_lr, mp, vp, sp), _torch_adam(O.v, O.vf_lr, mv, vv, sv)
+        O.ingest(*cols)
+        free.ingest(*cols)
+        L.ingest(*cols)
+        n, ne = L.finish()
+        assert ne == 8 and np.array_equal(L.offsets(), np.asarray(O.offsets))          # bit-exact segmentation
+        np.testing.assert_allclose(L.returns(n), O.ret[:n], rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(L.advantages(n, False), O.adv[:n], rtol=1e-6, atol=1e-6)
+        ref = O.train()
+        free.train()
+        st = L.train_epoch()
+        np.testing.assert_allclose(st["loss_pi"], ref["LossPi"], rtol=1e-5, atol=1e-6, err_msg="epoch %d" % ep)
+        np.testing.assert_allclose(st["loss_v"], ref["LossV"], rtol=1e-5, err_msg="epoch %d" % ep)
+        np.testing.assert_allclose(st["loss_v_old"], ref["LossVOld"], rtol=1e-5, err_msg="epoch %d" % ep)
+        np.testing.assert_allclose(st["kl"], ref["KL"], rtol=1e-5, atol=1e-6)
+        seen[0] = assert_weights_close(L.get_params(0), lo.flatten(ref["pi_params"]).numpy(), 3e-4, L, 0, set())
+        seen[1] = assert_weights_close(L.get_params(1), lo.flatten(ref["v_params"]).numpy(), 1e-3, L, 1, set())
+    drift = np.abs(L.get_params(1) - lo.flatten(free.v).numpy()).max()
+    print("H=%d: free-running oracle after %d epochs differs by at most %.3g (value weights)" % (H, epochs, drift))
+    assert drift < 1e-2
+    L.close()
+
+
+def test_c1_plugin_under_the_worker_pipe(tmp_path):
+    script = pd.REF_WORKER if os.path.exists(pd.REF_WORKER) else pd.STANDIN_WORKER
+    model = str(tmp_path / "server_model.pt")
+    cfg = str(tmp_path / "relayrl_config.json")
+    pd.write_config(cfg, model, traj_per_epoch=8, train_vf_iters=80)
+    w = pd.Worker(script, "REINFORCE_B200", pd.B200_ALGO_DIR, str(tmp_path), cfg, 4, 2, 8 * 500 + 8)
+    assert w.ready, w.stderr()[-3000:]
+    assert w.save_model() == {"status": "success"}            # the initial weights (seeded by PID, Q12)
+    m0 = torch.jit.load(model)
+    sd = m0.state_dict()
+    pi0 = [sd["policy.pi_network.%d.%s" % (i, k)].clone() for i in (0, 2, 4) for k in ("weight", "bias")]
+    v0 = [sd["baseline.v_network.%d.%s" % (i, k)].clone() for i in (0, 2, 4) for k in ("weight", "bias")]
+    O = lo.OracleLearner(4, 2, 8 * 500 + 8, hidden=128, with_baseline=True, train_vf_iters=80, seed=1)
+    O.pi, O.v = [p.requires_grad_(True) for p in pi0], [p.requires_grad_(True) for p in v0]
+    rng = np.random.default_rng(2)
+    for ep in range(3):
+        for t in range(8):
+            acts = pd.c1_trajectory(rng, hi=200)
+            O.ingest(*pd.actions_to_columns(acts, 4, 2))
+            reply = w.receive_trajectory(acts)
+            assert reply == ({"status": "success"} if t == 7 else {"status": "not_updated"}), (ep, t, reply, w.stderr()[-2000:])
+        O.train()
+        assert w.save_model() == {"status": "success"}
+        m = torch.jit.load(model)                               # what agents validate (agent_wrapper.rs:88-168)
+        assert m.get_input_dim() == 4 and m.get_output_dim() == 2
+        act, data = m.step(torch.zeros(1, 4), torch.zeros(1, 2))
+        assert "logp_a" in data and "v" in data
+        sd = m.state_dict()
+        got = torch.cat([sd["baseline.v_network.%d.%s" % (i, k)].reshape(-1) for i in (0, 2, 4) for k in ("weight", "bias")])
+        # free-running over three epochs: still close to the oracle
+        np.testing.assert_allclose(got.numpy(), lo.flatten(O.v).numpy(), rtol=1e-4, atol=1e-5)
+    assert w.close() == 0
+    # stdout carried the marker, the replies, and nothing that parses as a reply
+    for ln in w.other_lines:
+        assert not ln.lstrip().startswith('{"status"'), ln
+    assert "initialised on cuda" in w.stderr()

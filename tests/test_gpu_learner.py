@@ -18,17 +18,27 @@ pytestmark = pytest.mark.gpu
 W_RTOL, W_ATOL = 1e-5, 5e-7
 
 
-def assert_weights_close(actual, desired, lr):
-    """rel 1e-5 + abs 5e-7 on >= 99.9 % of the parameters.  The rest are parameters whose gradient
-    is ~eps = 1e-8, where Adam's update lr*m/(sqrt(v)+eps) is ill-conditioned in g:
-    a 1e-6 relative change of such a gradient moves the weight by a few percent of one lr-sized
-    step.  They must stay within 10 % of one Adam step (0.1 * lr).  The reference itself moves by
-    7e-8 between MKL thread counts (tests/test_oracle.py)."""
+def assert_weights_close(actual, desired, lr, learner=None, which=None, excused=None):
+    """rel 1e-5 + abs 5e-7 on >= 99.9 % of the parameters, and every parameter within 2 % of one Adam step (0.02 lr).
+    The few that miss the strict bound are counted, printed, and must be the ill-conditioned ones: Adam's update
+    lr * m_hat / (sqrt(v_hat) + eps) stops being scale-invariant where sqrt(v_hat) ~ eps = 1e-8, so there a 1e-7 relative
+    wobble of the gradient (float32 summation order) moves the weight by a visible fraction of lr.  Measured on B200
+    (tools/diag_outliers.py, golden epochs): 0-2 such parameters of 17 k, sqrt(v_hat) between 3e-10 and 5e-8 against a
+    largest sqrt(v_hat) of 2e-2 .. 9e-2, error <= 0.009 lr.  With `learner` given, a NEW outlier must have
+    sqrt(v_hat) < 1e-5 of the largest; `excused` carries outliers of earlier epochs (the error stays, v_hat grows)."""
     actual, desired = np.asarray(actual), np.asarray(desired)
     err = np.abs(actual - desired)
-    strict = err <= W_ATOL + W_RTOL * np.abs(desired)
-    assert strict.mean() >= 0.999, "only %.4f%% of parameters within rel 1e-5 + abs 5e-7" % (100 * strict.mean())
-    np.testing.assert_allclose(actual, desired, rtol=W_RTOL, atol=0.1 * lr)
+    out = set(np.flatnonzero(err > W_ATOL + W_RTOL * np.abs(desired)).tolist())
+    print("weights: %d of %d outside rel 1e-5 + abs 5e-7; largest error %.3g lr" % (len(out), len(actual), err.max() / lr))
+    assert len(out) <= max(2, len(actual) // 1000), "%d parameters outside rel 1e-5 + abs 5e-7" % len(out)
+    np.testing.assert_allclose(actual, desired, rtol=W_RTOL, atol=0.02 * lr)
+    if learner is not None:
+        m, v, step = learner.get_opt_state(which)
+        sv = np.sqrt(v / (1.0 - 0.999 ** step))
+        for i in sorted(out - (excused or set())):
+            assert sv[i] < 1e-5 * sv.max(), "parameter %d misses the bound with a healthy sqrt(v_hat) = %.3g (max %.3g)" % (
+                i, sv[i], sv.max())
+    return out | (excused or set())
 
 
 def _mk(g, iters=None):
@@ -53,6 +63,7 @@ def _ingest_epoch(L, g, ep):
 def test_epoch_golden(name):
     g = load_golden(name)
     L, d, A, H, wb = _mk(g)
+    seen_pi, seen_v = set(), set()
     for ep in range(int(g["epochs"])):
         p = "e%d_" % ep
         _ingest_epoch(L, g, ep)
@@ -67,11 +78,11 @@ def test_epoch_golden(name):
         np.testing.assert_allclose(st["kl"], float(g[p + "KL"]), rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(st["entropy"], float(g[p + "Entropy"]), rtol=1e-5, atol=1e-7)
         assert st["delta_loss_pi"] == 0.0
-        assert_weights_close(L.get_params(0), g[p + "pi"], float(g["pi_lr"]))
+        seen_pi = assert_weights_close(L.get_params(0), g[p + "pi"], float(g["pi_lr"]), L, 0, seen_pi)
         if wb:
             np.testing.assert_allclose(st["loss_v"], float(g[p + "LossV"]), rtol=1e-5)
             np.testing.assert_allclose(st["delta_loss_v"], float(g[p + "DeltaLossV"]), rtol=1e-4, atol=1e-6)
-            assert_weights_close(L.get_params(1), g[p + "v"], float(g["vf_lr"]))
+            seen_v = assert_weights_close(L.get_params(1), g[p + "v"], float(g["vf_lr"]), L, 1, seen_v)
     L.close()
 
 
