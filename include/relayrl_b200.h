@@ -131,6 +131,15 @@ int32_t rrl_get_params(rrl_learner_t *h, int32_t which, float *flat, int64_t n);
 int32_t rrl_get_opt_state(rrl_learner_t *h, int32_t which, float *m, float *v, int64_t n, int64_t *step);
 int32_t rrl_set_opt_state(rrl_learner_t *h, int32_t which, const float *m, const float *v, int64_t n, int64_t step);
 
+/* Checkpoint / resume of the training state (both networks' parameters, Adam moments and step counts, plus a caller tag
+ * such as the epoch counter) in one file, written atomically (temp file + rename).  No counterpart in the reference: a
+ * restarted server starts from fresh weights (src/network/server/training_zmq.rs:322-465), only the TorchScript policy is
+ * ever saved (REINFORCE.py:64-68).  Take it between epochs (the replay buffer is not saved).  A run resumed from a
+ * checkpoint continues bit-identically to the uninterrupted run.  Load fails with RRL_EFORMAT / RRL_EINVAL -- and leaves
+ * the learner untouched -- when the file is damaged or was written for other dimensions. */
+int32_t rrl_checkpoint_save(rrl_learner_t *h, const char *path, uint64_t user_tag);
+int32_t rrl_checkpoint_load(rrl_learner_t *h, const char *path, uint64_t *user_tag);
+
 /* receive_trajectory's per-action loop + ReplayBuffer.store (REINFORCE.py:70-87,
  * replay_buffer.py:34-46): packs rows into pinned staging, copies asynchronously into the flat
  * device buffers, records episode offsets (successive path_start_idx values) on the host. */

@@ -105,7 +105,8 @@ class _TsvLogger:
 
 
 class REINFORCE_B200(AlgorithmAbstract):
-    def __init__(self, env_dir, config_path, obs_dim, act_dim, buf_size, hidden=128, device=0, **extra):
+    def __init__(self, env_dir, config_path, obs_dim, act_dim, buf_size, hidden=128, device=0, checkpoint_path=None,
+                 **extra):
         super().__init__()
         hp, self.save_model_path = _load_hyperparams(config_path)
         self._with_vf_baseline = bool(hp["with_vf_baseline"])
@@ -138,6 +139,14 @@ class REINFORCE_B200(AlgorithmAbstract):
         self.traj = 0
         self.epoch = 0
         self.last_stats = None
+        # training-state checkpoint (the reference restarts from fresh weights,
+        # training_zmq.rs:322-465): an extra hyper-parameter names the file; it is loaded when present and rewritten
+        # after every epoch
+        self._checkpoint_path = checkpoint_path
+        if checkpoint_path and os.path.exists(checkpoint_path):
+            self.epoch = int(self.learner.checkpoint_load(checkpoint_path))
+            self.traj = self.epoch * self._traj_per_epoch
+            print("[REINFORCE_B200] resumed from %s at epoch %d" % (checkpoint_path, self.epoch), file=sys.stderr)
         print("[REINFORCE_B200] initialised on cuda:%d" % int(device), file=sys.stderr)
 
     # -- REINFORCE.save (REINFORCE.py:64-68) ------------------------------------------------------
@@ -172,6 +181,8 @@ class REINFORCE_B200(AlgorithmAbstract):
             self.epoch += 1
             self.train_model()
             self.log_epoch()
+            if self._checkpoint_path:
+                self.learner.checkpoint_save(self._checkpoint_path, tag=self.epoch)
             return True
         return False
 

@@ -2,7 +2,9 @@
 #include <stdarg.h>
 #include <string.h>
 
-#include "learner.cuh"
+#include <vector>
+
+#include "wire.h"
 
 namespace rrl {
 
@@ -658,3 +660,100 @@ int32_t rrl_get_adv_stats(rrl_learner_t *h, float *mean, float *std)
 }
 
 }  // extern "C"
+
+// ---- checkpoint / resume of the training state --------------------------------------
+// The reference keeps nothing across a restart: disable/enable/restart_server re-spawn the worker with a fresh
+// algorithm (src/network/server/training_zmq.rs:322-465) and only the TorchScript policy is ever written
+// (REINFORCE.py:64-68; utils/logger.py:200-269 save_state is never called).  One flat little-endian file:
+//   "RRLCKPT1" | i32 obs_dim, act_dim, hidden, with_baseline | u64 user_tag (the caller's epoch counter)
+//   per network (policy, then value when with_baseline): i64 n_params, i64 adam_step, f32 params[n], m[n], v[n]
+// The replay buffer is not part of it: a checkpoint is taken between epochs, where the buffer is empty by
+// construction (ReplayBuffer.get() resets it).
+namespace {
+const char CKPT_MAGIC[8] = {'R', 'R', 'L', 'C', 'K', 'P', 'T', '1'};
+}
+
+extern "C" int32_t rrl_checkpoint_save(rrl_learner_t *h, const char *path, uint64_t user_tag)
+{
+    H_CHECK(h);
+    if (!path) return RRL_EINVAL;
+    return abi_guard(h->err, "rrl_checkpoint_save", [&]() -> int32_t {
+        const std::string tmp = std::string(path) + ".tmp";
+        FILE *f = fopen(tmp.c_str(), "wb");
+        if (!f) {
+            h->err.set("rrl_checkpoint_save: cannot open %s", tmp.c_str());
+            return RRL_EINVAL;
+        }
+        bool ok = fwrite(CKPT_MAGIC, 1, 8, f) == 8;
+        const int32_t dims[4] = {h->cfg.obs_dim, h->cfg.act_dim, h->cfg.hidden, h->cfg.with_baseline};
+        ok = ok && fwrite(dims, sizeof dims, 1, f) == 1 && fwrite(&user_tag, 8, 1, f) == 1;
+        int32_t st = RRL_OK;
+        for (int which = 0; which < (h->cfg.with_baseline ? 2 : 1) && ok && st == RRL_OK; ++which) {
+            NetState &net = which == 0 ? h->pi : h->vf;
+            const int64_t n = net.dims.n_params(), step = net.step;
+            std::vector<float> buf((size_t)n * 3);
+            st = rrl_get_params(h, which, buf.data(), n);
+            if (st == RRL_OK) st = rrl_get_opt_state(h, which, buf.data() + n, buf.data() + 2 * n, n, nullptr);
+            ok = ok && fwrite(&n, 8, 1, f) == 1 && fwrite(&step, 8, 1, f) == 1 && fwrite(buf.data(), 4, buf.size(), f) == buf.size();
+        }
+        ok = (fclose(f) == 0) && ok;
+        if (st != RRL_OK || !ok || rename(tmp.c_str(), path) != 0) {  // written beside, renamed over: never a torn file
+            remove(tmp.c_str());
+            if (st == RRL_OK) h->err.set("rrl_checkpoint_save: write to %s failed", path);
+            return st != RRL_OK ? st : RRL_EINVAL;
+        }
+        return RRL_OK;
+    });
+}
+
+extern "C" int32_t rrl_checkpoint_load(rrl_learner_t *h, const char *path, uint64_t *user_tag)
+{
+    H_CHECK(h);
+    if (!path) return RRL_EINVAL;
+    return abi_guard(h->err, "rrl_checkpoint_load", [&]() -> int32_t {
+        FILE *f = fopen(path, "rb");
+        if (!f) {
+            h->err.set("rrl_checkpoint_load: cannot open %s", path);
+            return RRL_EINVAL;
+        }
+        char magic[8];
+        int32_t dims[4];
+        uint64_t tag = 0;
+        bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, CKPT_MAGIC, 8) == 0 && fread(dims, sizeof dims, 1, f) == 1 &&
+                  fread(&tag, 8, 1, f) == 1;
+        if (ok && (dims[0] != h->cfg.obs_dim || dims[1] != h->cfg.act_dim || dims[2] != h->cfg.hidden ||
+                   (dims[3] != 0) != (h->cfg.with_baseline != 0))) {
+            fclose(f);
+            h->err.set("rrl_checkpoint_load: %s holds obs_dim=%d act_dim=%d hidden=%d baseline=%d, this learner %d/%d/%d/%d", path,
+                       dims[0], dims[1], dims[2], dims[3], h->cfg.obs_dim, h->cfg.act_dim, h->cfg.hidden, h->cfg.with_baseline);
+            return RRL_EINVAL;
+        }
+        // read everything first, apply only when the whole file is sound
+        std::vector<float> bufs[2];
+        int64_t steps[2] = {0, 0};
+        const int nets = h->cfg.with_baseline ? 2 : 1;
+        for (int which = 0; which < nets && ok; ++which) {
+            const int64_t want = (which == 0 ? h->pi : h->vf).dims.n_params();
+            int64_t n = 0;
+            ok = fread(&n, 8, 1, f) == 1 && fread(&steps[which], 8, 1, f) == 1 && n == want && steps[which] >= 0;
+            if (ok) {
+                bufs[which].resize((size_t)n * 3);
+                ok = fread(bufs[which].data(), 4, bufs[which].size(), f) == bufs[which].size();
+            }
+        }
+        char extra;
+        ok = ok && fread(&extra, 1, 1, f) == 0;  // nothing may follow
+        fclose(f);
+        if (!ok) {
+            h->err.set("rrl_checkpoint_load: %s is not a checkpoint of this library (bad magic, sizes or truncated)", path);
+            return RRL_EFORMAT;
+        }
+        for (int which = 0; which < nets; ++which) {
+            const int64_t n = (int64_t)bufs[which].size() / 3;
+            RRL_TRY(rrl_set_params(h, which, bufs[which].data(), n));
+            RRL_TRY(rrl_set_opt_state(h, which, bufs[which].data() + n, bufs[which].data() + 2 * n, n, steps[which]));
+        }
+        if (user_tag) *user_tag = tag;
+        return RRL_OK;
+    });
+}

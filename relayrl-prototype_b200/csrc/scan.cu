@@ -124,7 +124,7 @@ __device__ unsigned long long g_scan_timing[16];
 #define SCT(slot, cond)                                                                          \
     do {                                                                                         \
         const long long sct_now = clock64();                                                     \
-        if (blockIdx.x == 0 && (cond)) atomicAdd(&g_scan_timing[slot], (unsigned long long)(sct_now - sct_prev)); \
+        if (blockIdx.x == gridDim.x / 2 && (cond)) atomicAdd(&g_scan_timing[slot], (unsigned long long)(sct_now - sct_prev)); \
         sct_prev = sct_now;                                                                      \
     } while (0)
 #else
@@ -424,6 +424,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 }
             }
         }
+        SCT(6, sct_me);  // pass 2: arithmetic
         float *ap = a.adv + t0 + j0, *rp = a.ret + t0 + j0;
         if (full || j0 + SCAN_VPT <= cnt) {
             st_stream4(ap, ao[0], ao[1], ao[2], ao[3]);
@@ -436,6 +437,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 if (j0 + k < cnt) ap[k] = ao[k], rp[k] = ro[k];
         }
     }
+    SCT(7, sct_me);  // pass 2: stores
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, d);
@@ -497,7 +499,7 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
         SCT(11, tid == SCAN_THREADS);     // producer waiting for the consumers
         SCT(12, tid == 32);               // (tile count: every span adds ~0, used as a divisor via slot 13)
 #ifdef SCAN_TIMING
-        if (blockIdx.x == 0 && tid == 32) atomicAdd(&g_scan_timing[13], 1ull);
+        if (blockIdx.x == gridDim.x / 2 && tid == 32) atomicAdd(&g_scan_timing[13], 1ull);
 #endif
         prev_tile = tile;
         b ^= 1;

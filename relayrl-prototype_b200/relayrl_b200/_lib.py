@@ -60,6 +60,8 @@ SIGNATURES = {
     "rrl_get_params": (C.c_int32, [_P, C.c_int32, _P, C.c_int64]),
     "rrl_get_opt_state": (C.c_int32, [_P, C.c_int32, _P, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "rrl_set_opt_state": (C.c_int32, [_P, C.c_int32, _P, _P, C.c_int64, C.c_int64]),
+    "rrl_checkpoint_save": (C.c_int32, [_P, C.c_char_p, C.c_uint64]),
+    "rrl_checkpoint_load": (C.c_int32, [_P, C.c_char_p, C.POINTER(C.c_uint64)]),
     "rrl_ingest_packed": (C.c_int32, [_P, C.POINTER(BatchView)]),
     "rrl_ingest_device": (C.c_int32, [_P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P, C.c_int64]),
     "rrl_ingest_wire_action": (C.c_int32, [_P, _P, C.c_size_t, _P, C.c_size_t, _P, C.c_size_t, C.c_float,

@@ -6,6 +6,7 @@ store-like ingest (`ingest`), `finish` (= every pending ReplayBuffer.finish_path
 relative to relayrl_framework/src/native/python/algorithms/REINFORCE/.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -97,6 +98,16 @@ class Learner:
     def set_opt_state(self, which, m, v, step):
         m, v = np.ascontiguousarray(m, np.float32), np.ascontiguousarray(v, np.float32)
         self._ck(self._L.rrl_set_opt_state(self._h, which, _ptr(m), _ptr(v), m.size, step))
+
+    def checkpoint_save(self, path, tag=0):
+        """Parameters + Adam state of both networks + `tag` (e.g. the epoch counter) -> one file, atomically."""
+        self._ck(self._L.rrl_checkpoint_save(self._h, os.fsencode(path), int(tag)))
+
+    def checkpoint_load(self, path):
+        """Restores what checkpoint_save wrote; returns the tag."""
+        tag = C.c_uint64()
+        self._ck(self._L.rrl_checkpoint_load(self._h, os.fsencode(path), C.byref(tag)))
+        return tag.value
 
     # -- ingest (REINFORCE.receive_trajectory's loop + ReplayBuffer.store, REINFORCE.py:70-87) ---
     def ingest(self, obs, act, mask, rew, val, logp, done):

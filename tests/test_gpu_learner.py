@@ -30,6 +30,11 @@ def assert_weights_close(actual, desired, lr, learner=None, which=None, excused=
     err = np.abs(actual - desired)
     out = set(np.flatnonzero(err > W_ATOL + W_RTOL * np.abs(desired)).tolist())
     print("weights: %d of %d outside rel 1e-5 + abs 5e-7; largest error %.3g lr" % (len(out), len(actual), err.max() / lr))
+    if out and learner is not None:   # what the offenders look like (shown with pytest -s or on failure)
+        m_, v_, step_ = learner.get_opt_state(which)
+        for i in sorted(out, key=lambda k: -err[k])[:8]:
+            print("   parameter %d: got %.9g want %.9g err %.3g lr, m %.3g v %.3g (step %d)" % (
+                i, actual[i], desired[i], err[i] / lr, m_[i], v_[i], step_))
     assert len(out) <= max(2, len(actual) // 1000), "%d parameters outside rel 1e-5 + abs 5e-7" % len(out)
     np.testing.assert_allclose(actual, desired, rtol=W_RTOL, atol=0.02 * lr)
     if learner is not None:

@@ -1,4 +1,4 @@
-"""Developer probe: phase breakdown of the scan kernel (CTA 0) from a -DSCAN_TIMING build.
+"""Developer probe: phase breakdown of the scan kernel (the middle CTA) from a -DSCAN_TIMING build.
 Usage: RELAYRL_B200_SO=tools/_timing/librelayrl_b200_timing.so python tools/scan_timing.py [N]"""
 import ctypes as C
 import os
@@ -28,7 +28,7 @@ L.rrl_debug_scan_timing(None, 1)
 ms = bench.measure_scan(cols, offsets, last_vals, n, dev, reps=5)
 L.rrl_debug_scan_timing(out, 0)
 names = {0: "consumer: loads + pass 1", 1: "consumer: warp scan", 2: "consumer: barrier 1", 3: "consumer: combine + look-back wait",
-         4: "consumer: pass 2 + stores", 5: "consumer: wait for producer", 8: "producer: issue copies", 9: "producer: search + mask",
+         6: "consumer: pass 2 arithmetic", 7: "consumer: pass 2 stores", 4: "consumer: pass 2 statistics reduce", 5: "consumer: wait for producer", 8: "producer: issue copies", 9: "producer: search + mask",
          10: "producer: wait for data", 11: "producer: wait for consumers"}
 tiles = max(out[13], 1)
 print("scan %.3f ms, %d tiles by CTA 0 (over 8 launches)" % (ms, tiles))
