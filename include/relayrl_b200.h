@@ -11,6 +11,12 @@
  * every algorithm call behind one asyncio.Lock, src/native/python/python_algorithm_reply.py:66,77,100)
  * but may come from different OS threads; every call selects the handle's device itself.
  * Different handles are independent.
+ *
+ * Data parallel (nranks > 1): rrl_finish, rrl_train_epoch, rrl_eval_grad and the parity taps that finish implicitly
+ * (rrl_get_returns, rrl_get_advantages, rrl_get_adv_stats) are COLLECTIVE: every rank must make the same call in the same
+ * order, like any NCCL program.  A rank that fails locally before the collective (RRL_ECAPACITY, RRL_ESTATE, a CUDA
+ * error) returns its status at once and the other ranks would wait for it: treat any non-zero status of these calls as
+ * fatal for the job and tear every rank down (the reference has no multi-process learner to mirror here).
  */
 #ifndef RELAYRL_B200_H
 #define RELAYRL_B200_H
@@ -144,7 +150,13 @@ int32_t rrl_checkpoint_load(rrl_learner_t *h, const char *path, uint64_t *user_t
  * replay_buffer.py:34-46): packs rows into pinned staging, copies asynchronously into the flat
  * device buffers, records episode offsets (successive path_start_idx values) on the host. */
 int32_t rrl_ingest_packed(rrl_learner_t *h, const rrl_batch_view_t *batch);
-/* Same, with device-resident SoA f32 inputs already free of terminal markers: `offsets`
+/* Same, with device-resident SoA f32 inputs already free of terminal markers.  Stream contract: the copies run on the
+ * learner's own stream (rrl_learner_stream), ordered AFTER everything queued on the legacy default stream (stream 0)
+ * at the time of the call, and work queued on stream 0 after the call waits for them -- so a caller that fills and
+ * frees its buffers on the default stream (torch's default) needs no synchronisation.  A caller working on another
+ * stream must make its inputs complete before the call (e.g. cudaStreamSynchronize, or an event the default stream
+ * waits on) and keep them alive until rrl_learner_stream has been synchronised.  rrl_actor_step_device orders its
+ * inputs the same way and returns with its outputs complete.  `offsets`
  * (n_ep + 1 entries relative to this batch, offsets[0] == 0) and `last_vals` (n_ep) are host arrays. */
 int32_t rrl_ingest_device(rrl_learner_t *h, const float *obs, const float *act, const float *mask,
                           const float *rew, const float *val, const float *logp, int64_t count,

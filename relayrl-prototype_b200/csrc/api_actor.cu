@@ -21,6 +21,7 @@ int32_t rrl_actor_destroy(rrl_actor_t *a)
     cudaFree(a->pi_params), cudaFree(a->pi_w1p), cudaFree(a->vf_params), cudaFree(a->vf_w1p);
     cudaFree(a->d_obs), cudaFree(a->d_mask), cudaFree(a->d_logp), cudaFree(a->d_v), cudaFree(a->d_probs);
     cudaFree(a->d_logits), cudaFree(a->d_act);
+    if (a->order_ev) cudaEventDestroy(a->order_ev);
     if (a->stream) cudaStreamDestroy(a->stream);
     delete a;
     return RRL_OK;
@@ -51,6 +52,7 @@ int32_t rrl_actor_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32
     const NetDims pd{obs_dim, hidden, act_dim}, vd{obs_dim, hidden, 1};
     const size_t dK = (obs_dim + 3) & ~3, B = (size_t)max_batch;
     bool ok = cudaStreamCreateWithFlags(&a->stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&a->order_ev, cudaEventDisableTiming) == cudaSuccess;
     auto al = [&](void **p, size_t bytes) {
         if (ok) ok = cudaMalloc(p, bytes) == cudaSuccess && cudaMemset(*p, 0, bytes) == cudaSuccess;
     };
@@ -96,10 +98,11 @@ int32_t rrl_actor_step_device(rrl_actor_t *a, const float *obs, const float *mas
         a->err.set("rrl_actor_step_device: null pointer");
         return RRL_EINVAL;
     }
+    if (a->order_ev) RRL_CUDA_OK(order_after_default_stream(a->stream, a->order_ev), a->err);  // inputs made on stream 0
     RRL_TRY(actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->d,
                                  a->H, a->A, obs, mask, batch, seed, offset, force_act, act, logp_a, v, probs, logits,
                                  a->stream, a->err));
-    RRL_CUDA_OK(cudaStreamSynchronize(a->stream), a->err);
+    RRL_CUDA_OK(cudaStreamSynchronize(a->stream), a->err);  // outputs are complete when the call returns
     return RRL_OK;
 }
 

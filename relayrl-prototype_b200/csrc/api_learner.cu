@@ -215,6 +215,7 @@ int32_t learner_finish(rrl_learner *h)
                         h->cfg.with_baseline != 0, h->adv, h->ret, h->stats, h->scan_ws, h->scan_ws_bytes, single,
                         h->offsets.back(), st, h->err, &h->launches));
     h->n_global = h->ptr, h->ep_global = n_ep;
+    h->high_water = std::max(h->high_water, h->ptr);
     if (!single) {
         // (sum, sumsq, n, n_ep) of every rank, merged in rank order on every rank => identical mean/std
         const double nep = (double)n_ep;
@@ -569,7 +570,8 @@ int32_t rrl_ingest_device(rrl_learner_t *h, const float *obs, const float *act, 
     const int d = h->cfg.obs_dim, A = h->cfg.act_dim;
     const int64_t base = h->ptr;
     cudaStream_t st = h->stream;
-    // the caller's buffers live on the default stream's timeline: make them visible first
+    // the caller's buffers live on the default stream's timeline: the copies start after what is queued there ...
+    RRL_CUDA_OK(order_after_default_stream(st, h->ev[5]), h->err);
     RRL_CUDA_OK(cudaMemcpyAsync(h->obs + base * d, obs, (size_t)count * d * 4, cudaMemcpyDeviceToDevice, st), h->err);
     RRL_CUDA_OK(cudaMemcpyAsync(h->mask + base * A, mask, (size_t)count * A * 4, cudaMemcpyDeviceToDevice, st), h->err);
     RRL_CUDA_OK(cudaMemcpyAsync(h->act + base, act, (size_t)count * 4, cudaMemcpyDeviceToDevice, st), h->err);
@@ -577,6 +579,8 @@ int32_t rrl_ingest_device(rrl_learner_t *h, const float *obs, const float *act, 
     RRL_CUDA_OK(cudaMemcpyAsync(h->logp + base, logp, (size_t)count * 4, cudaMemcpyDeviceToDevice, st), h->err);
     if (h->cfg.with_baseline)
         RRL_CUDA_OK(cudaMemcpyAsync(h->val + base, val, (size_t)count * 4, cudaMemcpyDeviceToDevice, st), h->err);
+    // ... and whatever the caller queues there next (a free, a refill of these buffers) waits for the copies
+    RRL_CUDA_OK(order_default_stream_after(st, h->ev[6]), h->err);
     for (int64_t e = 1; e <= n_ep; ++e) {
         if (offsets[e] < offsets[e - 1]) {
             h->err.set("rrl_ingest_device: offsets not monotone at %lld", (long long)e);
@@ -667,8 +671,11 @@ int32_t rrl_get_adv_stats(rrl_learner_t *h, float *mean, float *std)
 // (REINFORCE.py:64-68; utils/logger.py:200-269 save_state is never called).  One flat little-endian file:
 //   "RRLCKPT1" | i32 obs_dim, act_dim, hidden, with_baseline | u64 user_tag (the caller's epoch counter)
 //   per network (policy, then value when with_baseline): i64 n_params, i64 adam_step, f32 params[n], m[n], v[n]
-// The replay buffer is not part of it: a checkpoint is taken between epochs, where the buffer is empty by
-// construction (ReplayBuffer.get() resets it).
+//   i64 high_water, f32 adv[high_water], ret[high_water]
+// A checkpoint is taken between epochs, where the replay buffer is empty (ReplayBuffer.get() resets it) -- except for
+// one thing the reference's buffer carries across epochs: adv/ret are never re-zeroed, and transitions stored after an
+// epoch's last terminal marker train on whatever those slots held before.  So the stale adv/ret contents
+// up to the largest fill level seen are part of the state; without them a resumed run with unfinished tails diverges.
 namespace {
 const char CKPT_MAGIC[8] = {'R', 'R', 'L', 'C', 'K', 'P', 'T', '1'};
 }
@@ -695,6 +702,18 @@ extern "C" int32_t rrl_checkpoint_save(rrl_learner_t *h, const char *path, uint6
             st = rrl_get_params(h, which, buf.data(), n);
             if (st == RRL_OK) st = rrl_get_opt_state(h, which, buf.data() + n, buf.data() + 2 * n, n, nullptr);
             ok = ok && fwrite(&n, 8, 1, f) == 1 && fwrite(&step, 8, 1, f) == 1 && fwrite(buf.data(), 4, buf.size(), f) == buf.size();
+        }
+        if (ok && st == RRL_OK) {
+            const int64_t hw = h->high_water;
+            std::vector<float> buf((size_t)hw * 2 + 1);
+            cudaError_t ce = cudaMemcpyAsync(buf.data(), h->adv, (size_t)hw * 4, cudaMemcpyDeviceToHost, h->stream);
+            if (ce == cudaSuccess) ce = cudaMemcpyAsync(buf.data() + hw, h->ret, (size_t)hw * 4, cudaMemcpyDeviceToHost, h->stream);
+            if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->stream);
+            if (ce != cudaSuccess) {
+                h->err.set("rrl_checkpoint_save: reading adv/ret failed: %s", cudaGetErrorString(ce));
+                st = RRL_ECUDA;
+            }
+            ok = fwrite(&hw, 8, 1, f) == 1 && fwrite(buf.data(), 4, (size_t)hw * 2, f) == (size_t)hw * 2;
         }
         ok = (fclose(f) == 0) && ok;
         if (st != RRL_OK || !ok || rename(tmp.c_str(), path) != 0) {  // written beside, renamed over: never a torn file
@@ -741,6 +760,13 @@ extern "C" int32_t rrl_checkpoint_load(rrl_learner_t *h, const char *path, uint6
                 ok = fread(bufs[which].data(), 4, bufs[which].size(), f) == bufs[which].size();
             }
         }
+        int64_t hw = 0;
+        std::vector<float> stale;
+        ok = ok && fread(&hw, 8, 1, f) == 1 && hw >= 0 && hw <= h->cfg.capacity;
+        if (ok) {
+            stale.resize((size_t)hw * 2 + 1);
+            ok = fread(stale.data(), 4, (size_t)hw * 2, f) == (size_t)hw * 2;
+        }
         char extra;
         ok = ok && fread(&extra, 1, 1, f) == 0;  // nothing may follow
         fclose(f);
@@ -753,6 +779,10 @@ extern "C" int32_t rrl_checkpoint_load(rrl_learner_t *h, const char *path, uint6
             RRL_TRY(rrl_set_params(h, which, bufs[which].data(), n));
             RRL_TRY(rrl_set_opt_state(h, which, bufs[which].data() + n, bufs[which].data() + 2 * n, n, steps[which]));
         }
+        RRL_CUDA_OK(cudaMemcpyAsync(h->adv, stale.data(), (size_t)hw * 4, cudaMemcpyHostToDevice, h->stream), h->err);
+        RRL_CUDA_OK(cudaMemcpyAsync(h->ret, stale.data() + hw, (size_t)hw * 4, cudaMemcpyHostToDevice, h->stream), h->err);
+        RRL_CUDA_OK(cudaStreamSynchronize(h->stream), h->err);
+        h->high_water = hw;
         if (user_tag) *user_tag = tag;
         return RRL_OK;
     });

@@ -30,6 +30,7 @@ struct rrl_learner {
           *adv = nullptr, *ret = nullptr;
     float *tmp = nullptr;              // [capacity] scratch for the normalised-advantage tap
     int64_t ptr = 0;                   // ReplayBuffer.ptr
+    int64_t high_water = 0;            // largest ptr a scan has covered: adv/ret hold stale values up to here (Q7)
     std::vector<int64_t> offsets;      // successive path_start_idx values, offsets[0] = 0
     std::vector<float> last_vals;      // one per closed path
     int64_t *d_offsets = nullptr;
@@ -71,9 +72,24 @@ struct rrl_actor {
     // device mirrors of the host-facing buffers of rrl_actor_step
     float *d_obs = nullptr, *d_mask = nullptr, *d_logp = nullptr, *d_v = nullptr, *d_probs = nullptr, *d_logits = nullptr;
     int64_t *d_act = nullptr;
+    cudaEvent_t order_ev = nullptr;  // ordering against the caller's default stream (rrl_actor_step_device)
 };
 
 namespace rrl {
+// Device-pointer entry points run on the handle's own non-blocking stream, which is NOT implicitly ordered against the
+// stream the caller filled its buffers on.  These two calls order it against the legacy default stream (stream 0: where
+// torch and most plain CUDA code work): the library's work starts after everything queued there, and whatever the caller
+// queues there next -- a free, a reuse of the buffers -- starts after the library's reads.
+inline cudaError_t order_after_default_stream(cudaStream_t lib, cudaEvent_t ev)
+{
+    cudaError_t e = cudaEventRecord(ev, cudaStreamLegacy);
+    return e != cudaSuccess ? e : cudaStreamWaitEvent(lib, ev, 0);
+}
+inline cudaError_t order_default_stream_after(cudaStream_t lib, cudaEvent_t ev)
+{
+    cudaError_t e = cudaEventRecord(ev, lib);
+    return e != cudaSuccess ? e : cudaStreamWaitEvent(cudaStreamLegacy, ev, 0);
+}
 extern thread_local ErrBuf g_create_err;  // failures without a handle
 int32_t learner_flush_staging(rrl_learner *h);
 // all-or-nothing appends (wire decoders): where the replay buffer stood, and back to it

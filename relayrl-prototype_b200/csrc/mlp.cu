@@ -591,7 +591,11 @@ int32_t run_pass(NetState &net, const TrainBuffers &tb, int mode, bool with_grad
     int grid = (int)std::min<int64_t>(net.grid, std::max<int64_t>(tiles, 1));
     const size_t smem = mlp_smem_bytes(nd.d, nd.H, nd.out);
     int32_t st;
+#ifdef RRL_DEVTOOLS  // developer library only: force the CUDA-core kernel for A/B comparisons
     static const bool tc_off = getenv("RRL_DISABLE_TC") != nullptr;
+#else
+    constexpr bool tc_off = false;
+#endif
     if (!tc_off && tc_pass_supported(nd, mode, with_grad))
         st = tc_pass_launch(a, nd, mode, grid, stream, err);
     else if (mode == MODE_VALUE)

@@ -26,6 +26,8 @@
 //        straight from registers
 //     -> per-tile (sum, sum of squares) of the f32-rounded advantages in f64, fixed summation order.
 // Arithmetic is float64 with float32 storage, as in the reference.
+#include <cmath>
+
 #include "common.cuh"
 
 namespace rrl {
@@ -53,12 +55,20 @@ __device__ __forceinline__ bool is_unset(double x) { return __double_as_longlong
 __device__ __forceinline__ double2 ld_relaxed2(const double2 *p)
 {
     double2 v;
+#ifdef SCAN_POLL_CG  // developer experiment: L2-cached weak load instead of the strong (relaxed.gpu) one
+    asm volatile("ld.volatile.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+#else
     asm volatile("ld.relaxed.gpu.global.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p) : "memory");
+#endif
     return v;
 }
 __device__ __forceinline__ void st_relaxed2(double2 *p, double x, double y)
 {
+#ifdef SCAN_POLL_CG
+    asm volatile("st.volatile.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(x), "d"(y) : "memory");
+#else
     asm volatile("st.relaxed.gpu.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(x), "d"(y) : "memory");
+#endif
 }
 __device__ __forceinline__ void st_stream4(float *p, float a, float b, float c, float d)
 {
@@ -114,9 +124,11 @@ struct ScanCtl {  // consumer hand-offs inside one tile
     double2 wcarry[SCAN_WARPS];    // per warp: the carry that enters it from the right (after the look-back)
     double2 wstat[2][SCAN_WARPS];  // per warp: (sum, sum of squares); double buffered by tile parity
     unsigned wclosed[SCAN_WARPS];  // per warp: a path ends inside it
+    double2 chain[2];              // chunk mode: (ret, adv) at the first element of the tile this CTA did last (by parity)
     double2 tpow[32];              // tp^i (ret, adv), i = 0..31: the look-back's per-lane slopes (set once per CTA)
 };
 constexpr double SCAN_CUT = 1e-100;
+constexpr double SCAN_CUT_HOST = SCAN_CUT;
 
 #ifdef SCAN_TIMING  // developer build only: clock64 spans of CTA 0 (warp 1 of the consumers, lane 0; the producer's lane 0)
 __device__ unsigned long long g_scan_timing[16];
@@ -140,9 +152,33 @@ __device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gme
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(SCAN_THREADS) : "memory"); }
 
 // producer warp: claim the next tile and fill `B` for it (or mark it empty)
+// Chunk mode: a CTA's tiles follow each other to the left, so the boundaries it needs are consecutive entries of `offsets`
+// just below the previous tile's.  The producer keeps a 256-entry window of offsets / last_vals in shared memory and
+// refills it (one round trip) when a tile's neighbourhood leaves it, instead of two or three dependent L2 round trips
+// per tile.
+constexpr int SCAN_OC = 256;
+struct OffCache {
+    long long off[SCAN_OC];
+    float lv[SCAN_OC];
+};
+struct ProdState {
+    long long cursor = 0;  // the previous tile's first boundary index (0: none yet)
+    long long c0 = -1;     // offsets index of the window's first entry (-1: empty)
+    OffCache *win = nullptr;
+};
+
 template <bool WB>
-__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int64_t n_scan, int num_tiles, int lane, int j)
+__device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int64_t n_scan, int num_tiles, int lane, int j,
+                                             ProdState *ps = nullptr)
 {
+    long long *cursor = ps ? &ps->cursor : nullptr;
+    const long long c0 = ps ? ps->c0 : -1;
+    auto off_at = [&](long long k) -> long long {
+        return (c0 >= 0 && k >= c0 && k < c0 + SCAN_OC) ? ps->win->off[k - c0] : a.offsets[k];
+    };
+    auto lv_at = [&](long long k) -> float {
+        return (c0 >= 0 && k >= c0 && k < c0 + SCAN_OC) ? ps->win->lv[k - c0] : a.last_vals[k];
+    };
     // j: logical tile, 0 is the right-most
     SCT_DECL;
     const int tile = j < num_tiles ? num_tiles - 1 - j : -1;
@@ -159,9 +195,13 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
         cp_async16_zfill(&B.r[sidx(4 * c)], a.rew + g, valid);
         if (WB) cp_async16_zfill(&B.v[sidx(4 * c)], a.val + g, valid);
     }
+    if (WB && lane == 0) {  // the first value of the tile to the right (4-byte copy in the same group; zero beyond the end)
+        const bool in = t0 + SCAN_TILE < n_scan;
+        const unsigned sdst = (unsigned)__cvta_generic_to_shared(&B.v[sidx(SCAN_TILE)]);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(sdst), "l"(a.val + (in ? t0 + SCAN_TILE : 0)), "r"(in ? 4 : 0) : "memory");
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
     SCT(8, lane == 0);  // producer: issue
-    if (WB && lane == 0) B.v[sidx(SCAN_TILE)] = (t0 + SCAN_TILE < n_scan) ? a.val[t0 + SCAN_TILE] : 0.f;
 
 #ifdef SCAN_DBG_NO_SEARCH  // timing experiment only (wrong results)
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -169,6 +209,20 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
 #endif
     // first path boundary beyond t0: smallest e in [1, E] with offsets[e] > t0
     long long lo = 1, hi = a.n_ep;
+    if (cursor && *cursor > 0) {
+        // chunk mode: this tile lies directly to the left of the previous one, whose answer is *cursor -- walk down from
+        // it (one round of 32 probes covers the usual case; the 32-ary search below is for a CTA's first tile only)
+        lo = *cursor;
+        while (true) {
+            const long long p = lo - 1 - lane;
+            const bool gt = p >= 1 && off_at(p) > t0;
+            const unsigned b = __ballot_sync(0xffffffffu, gt);
+            const int run = b == 0xffffffffu ? 32 : __ffs(~b) - 1;  // offsets are sorted: the probes that pass form a prefix
+            lo -= run;
+            if (run < 32) break;
+        }
+        hi = lo;
+    }
     while (lo < hi) {
         const long long span = hi - lo;
         const long long p = lo + (span * (lane + 1)) / 33;
@@ -182,6 +236,7 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
             if (f > 0) lo = lo + (span * f) / 33 + 1;
         }
     }
+    if (cursor) *cursor = lo;
     __syncwarp();  // the zeroed mask words are visible to the whole warp before the atomics
     const int64_t t1 = t0 + cnt;
     for (long long k0 = lo; k0 <= a.n_ep; k0 += 128) {
@@ -192,18 +247,31 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
         for (int u = 0; u < 4; ++u) {
             const long long k = k0 + u * 32 + lane;
             if (k <= a.n_ep) {
-                const int64_t b = a.offsets[k];
+                const int64_t b = off_at(k);
                 if (b <= t1) {
                     if (u == 3) more = true;
-                    if (b > a.offsets[k - 1]) {  // a non-empty path ends at b-1
+                    if (b > off_at(k - 1)) {  // a non-empty path ends at b-1
                         const int pos = (int)(b - 1 - t0);
                         atomicOr(&B.end[pos >> 5], 1u << (pos & 31));
-                        B.lv[pos] = a.last_vals[k - 1];
+                        B.lv[pos] = lv_at(k - 1);
                     }
                 }
             }
         }
         if (!__any_sync(0xffffffffu, more)) break;  // offsets are sorted: nothing further can fall in the tile
+    }
+    if (ps && (c0 < 0 || lo - 33 < c0 || lo + 128 > c0 + SCAN_OC)) {
+        // the NEXT tile (to the left) probes [lo - 32, lo) and then reads up to 128 entries from its own answer upwards:
+        // re-centre the window so that both stay inside for the next ~90 boundaries
+        const long long n0 = lo - 120 > 0 ? lo - 120 : 0;
+        __syncwarp();
+        for (int i = lane; i < SCAN_OC; i += 32) {
+            const long long k = n0 + i;
+            ps->win->off[i] = k <= a.n_ep ? a.offsets[k] : 0x7fffffffffffffffll;
+            ps->win->lv[i] = k < a.n_ep ? a.last_vals[k] : 0.f;
+        }
+        ps->c0 = n0;
+        __syncwarp();
     }
     SCT(9, lane == 0);  // producer: search + mask
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -212,9 +280,12 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
 
 // consumer warps (threads 0..255): scan the tile in `B`, publish / look back, write the outputs.
 // lane_r / lane_a: c^(8 * (31 - lane)), the slope between the warp's right edge and this lane's right edge.
-template <bool WB>
+// CHUNK: the CTA walks a contiguous run of tiles, so the carry into a tile is the previous tile's value, kept in
+// shared memory (S.chain) -- no descriptors, no polling.  `warm`: a warm-up tile to the right of the CTA's run: only its
+// value at its first element is wanted (no outputs, no statistics).
+template <bool WB, bool CHUNK>
 __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan, int num_tiles,
-                                             ScanCtl &S, int tid, double lane_r, double lane_a, int parity)
+                                             ScanCtl &S, int tid, double lane_r, double lane_a, int parity, bool warm)
 {
     const int lane = tid & 31, warp = tid >> 5;
     SCT_DECL;
@@ -307,8 +378,10 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
     consumer_sync();
     SCT(2, sct_me);  // barrier 1
 
-    // ---- warp 0: the eight warps, the tile's descriptor, the look-back -------------------------------------
-    if (warp == 0) {
+    // ---- the eight warps; look-back kernel: warp 0 alone, with the tile's descriptor and the look-back; chunk kernel:
+    // every warp for itself (a dozen instructions), which saves the second barrier and the wait for warp 0 -------------
+    double wc_r = 0.0, wc_a = 0.0;  // the carry that enters this warp from the right
+    if (CHUNK || warp == 0) {
         double xr = 0.0, xa = 0.0;
         if (lane < SCAN_WARPS) xr = S.wagg[lane].x, xa = S.wagg[lane].y;
         const unsigned cm = __ballot_sync(0xffffffffu, lane < SCAN_WARPS && S.wclosed[lane] != 0u);  // warps with a path end
@@ -323,13 +396,19 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
         // lane 0: the whole tile
         const bool closed = cm != 0u;  // the value at the tile's first element does not depend on the carry-in
-        if (lane == 0) {
+        if (!CHUNK && lane == 0) {
             if (closed)
                 st_relaxed2(&a.incl[tile], xr, xa);
             else
                 st_relaxed2(&a.agg[tile], xr, xa);
         }
         double cr = 0.0, ca = 0.0;  // carry into the tile from the tiles to the right
+        if (CHUNK) {
+            const double2 prev = S.chain[parity ^ 1];  // the tile just done by this CTA: the value at its first element
+            if (open_right) cr = prev.x, ca = prev.y;
+            if (warp == 0 && lane == 0)
+                S.chain[parity] = closed ? make_double2(xr, xa) : make_double2(fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
+        } else
 #ifdef SCAN_DBG_NO_LOOKBACK  // timing experiment only (wrong results)
         if (false) {
 #else
@@ -376,7 +455,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 base += 32;
             }
         }
-        if (lane == 0 && !closed) st_relaxed2(&a.incl[tile], fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
+        if (!CHUNK && lane == 0 && !closed) st_relaxed2(&a.incl[tile], fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
         // carry into warp w: the warps to its right for a zero tile carry, plus the tile carry across them when open
         double nr = __shfl_down_sync(0xffffffffu, xr, 1), na = __shfl_down_sync(0xffffffffu, xa, 1);
         if (lane < SCAN_WARPS) {
@@ -386,19 +465,24 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 for (int i = lane; i < SCAN_WARPS - 1; ++i) qr *= a.wp_r, qa *= a.wp_a;
                 nr = fma(qr, cr, nr), na = fma(qa, ca, na);
             }
-            S.wcarry[lane] = make_double2(nr, na);
+            if (!CHUNK) S.wcarry[lane] = make_double2(nr, na);
         }
+        if (CHUNK) wc_r = __shfl_sync(0xffffffffu, nr, warp), wc_a = __shfl_sync(0xffffffffu, na, warp);
     }
-    consumer_sync();
+    if (!CHUNK) consumer_sync();
     SCT(3, sct_me);  // warp 0's combine + look-back (as seen by a waiting warp)
+    if (CHUNK && warm) return;
 
     // ---- pass 2: add the carry, round to f32, statistics, stores straight from registers -------------------------
     double s1 = 0.0, s2 = 0.0;
     {
         double cr = er, ca = ea;
         if (lane_open) {
-            const double2 wc = S.wcarry[warp];
-            cr = fma(lane_r, wc.x, cr), ca = fma(lane_a, wc.y, ca);
+            if (!CHUNK) {
+                const double2 wc = S.wcarry[warp];
+                wc_r = wc.x, wc_a = wc.y;
+            }
+            cr = fma(lane_r, wc_r, cr), ca = fma(lane_a, wc_a, ca);
         }
         float ao[SCAN_VPT], ro[SCAN_VPT];
         if (em == 0u && full) {
@@ -492,7 +576,7 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
         if (producer)
             scan_prepare<WB>(a, buf[b ^ 1], n_scan, num_tiles, lane, j);
         else
-            scan_consume<WB>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b);
+            scan_consume<WB, false>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, false);
         SCT_DECL;
         __syncthreads();
         SCT(5, tid == 32);                // consumers waiting for the producer
@@ -502,6 +586,59 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
         if (blockIdx.x == gridDim.x / 2 && tid == 32) atomicAdd(&g_scan_timing[13], 1ull);
 #endif
         prev_tile = tile;
+        b ^= 1;
+    }
+}
+
+// Chunk mode: CTA c owns the contiguous logical tiles [c K, (c + 1) K) and walks them right-to-left, so the carry
+// from tile to tile never leaves the CTA.  What comes in from the CTA's right-hand neighbour is recomputed instead of
+// waited for: the CTA first runs `warm` extra tiles to the right of its run through pass 1 only.  After W open tiles the
+// influence of anything further right is slope^W < SCAN_CUT (see the look-back cut-off: below 1e-56 in absolute terms,
+// eleven decades under the smallest f32 denormal), and a path end inside the warm-up makes it exact.  For gamma = 0.98
+// that is 6 tiles of reads for every ~74 tiles of work, no descriptors, no polling, no memset, no co-residency.  The
+// look-back kernel above stays for discounts so close to 1 that the warm-up would outgrow the run (scan_launch picks).
+template <bool WB>
+__global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_chunk_kernel(ScanArgs a, int tiles_per_cta, int warm)
+{
+    extern __shared__ __align__(16) unsigned char scan_dyn[];
+    TileBuf *buf = reinterpret_cast<TileBuf *>(scan_dyn);
+    __shared__ ScanCtl ctl;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool producer = tid >= SCAN_THREADS;
+    const int64_t n_scan = a.offsets[a.n_ep];
+    if (n_scan > a.n_total || n_scan < 0) return;
+    const int num_tiles = (int)((n_scan + SCAN_TILE - 1) / SCAN_TILE);
+    const int j_begin = blockIdx.x * tiles_per_cta, j_end = min(j_begin + tiles_per_cta, num_tiles);
+    if (j_begin >= num_tiles) return;
+    int j = max(j_begin - warm, 0);  // logical tile (0 = right-most); tiles before j_begin are warm-up
+
+    double lane_r = 1.0, lane_a = 1.0;  // c^(8 * (31 - lane))
+    for (int i = lane; i < 31; ++i) lane_r *= a.st_r[0], lane_a *= a.st_a[0];
+    if (tid == 0) ctl.chain[0] = ctl.chain[1] = make_double2(0.0, 0.0);
+    __shared__ OffCache win;
+    ProdState ps;
+    ps.win = &win;
+
+    if (producer) scan_prepare<WB>(a, buf[0], n_scan, j < j_end ? num_tiles : 0, lane, j, &ps);
+    __syncthreads();
+    int b = 0, prev_tile = -1;
+    while (true) {
+        const int tile = buf[b].tile;
+        if (tid == 0 && prev_tile >= 0) {  // the previous tile's statistics, eight warp sums in a fixed order
+            double t1 = 0.0, t2 = 0.0;
+            for (int w = 0; w < SCAN_WARPS; ++w) t1 += ctl.wstat[b ^ 1][w].x, t2 += ctl.wstat[b ^ 1][w].y;
+            a.partials[prev_tile] = make_double2(t1, t2);
+        }
+        if (tile < 0) break;
+        const bool is_warm = j < j_begin;
+        ++j;
+        if (producer)
+            scan_prepare<WB>(a, buf[b ^ 1], n_scan, j < j_end ? num_tiles : 0, lane, j, &ps);
+        else
+            scan_consume<WB, true>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, is_warm);
+        __syncthreads();
+        prev_tile = is_warm ? -1 : tile;
         b ^= 1;
     }
 }
@@ -688,14 +825,10 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
     a.partials = reinterpret_cast<double2 *>(base + w.partials);
     const int tiles = (int)((n_cover + SCAN_TILE - 1) / SCAN_TILE);
     if (tiles > 0) {
-        // every descriptor word starts as the "unset" sentinel; the same memset leaves the ticket counter at -1
-        RRL_CUDA_OK(cudaMemsetAsync(base, 0xFF, w.partials, stream), err);
         const size_t smem = 2 * sizeof(TileBuf);
-        static int per_sm_cached[2] = {0, 0}, sms_cached = 0;
-        const int which = with_baseline ? 1 : 0;
-        if (per_sm_cached[which] == 0) {
-            const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
-                                           : reinterpret_cast<const void *>(scan_kernel<false>);
+        static int per_sm_cached[4] = {0, 0, 0, 0}, sms_cached = 0;  // [chunk? 2 : 0] + with_baseline
+        auto occupancy = [&](const void *fn, int slot) -> int32_t {
+            if (per_sm_cached[slot]) return RRL_OK;
             RRL_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
             int dev = 0, sms = 0, per_sm = 0;
             RRL_CUDA_OK(cudaGetDevice(&dev), err);
@@ -705,14 +838,51 @@ int32_t scan_launch(const float *rew, const float *val, const int64_t *offsets, 
                 err.set("scan: kernel does not fit on an SM (%zu B shared memory)", smem);
                 return RRL_ECUDA;
             }
-            sms_cached = sms, per_sm_cached[which] = per_sm;
+            sms_cached = sms, per_sm_cached[slot] = per_sm;
+            return RRL_OK;
+        };
+        // Warm-up length of the chunk kernel: open tiles after which a carry has decayed below SCAN_CUT.
+        int warm = 1 << 30;
+        {
+            const double tp = std::max(a.tp_r, a.tp_a);
+            if (tp <= 0.0) {
+                warm = 1;
+            } else if (tp < 1.0) {
+                const double w_ = std::ceil(std::log(SCAN_CUT_HOST) / std::log(tp));
+                if (w_ < 1e6) warm = std::max(1, (int)w_);
+            }
         }
-        // co-resident by construction: the look-back spins on tiles owned by other CTAs
-        const int grid = std::min(tiles, per_sm_cached[which] * sms_cached);
-        const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
-                                       : reinterpret_cast<const void *>(scan_kernel<false>);
-        void *args[] = {&a};
-        RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SCAN_CTA_THREADS), args, smem, stream), err);
+        const int wb = with_baseline ? 1 : 0;
+        const void *fn_chunk = with_baseline ? reinterpret_cast<const void *>(scan_chunk_kernel<true>)
+                                             : reinterpret_cast<const void *>(scan_chunk_kernel<false>);
+        RRL_TRY(occupancy(fn_chunk, 2 + wb));
+        const int max_ctas = per_sm_cached[2 + wb] * sms_cached;
+        // a run is at least four warm-ups long (the warm-up then reads at most a quarter on top), even if that leaves
+        // CTA slots empty at small sizes; discounts whose warm-up exceeds 64 tiles (gamma > ~0.998) take the look-back
+        const int per_cta = std::max((tiles + max_ctas - 1) / max_ctas, std::min(4 * warm, tiles));
+#ifdef SCAN_FORCE_LOOKBACK
+        const bool chunk = false;
+#else
+        const bool chunk = warm <= 64;
+#endif
+        if (chunk) {
+            const int grid = (tiles + per_cta - 1) / per_cta;
+            if (with_baseline)
+                scan_chunk_kernel<true><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a, per_cta, warm);
+            else
+                scan_chunk_kernel<false><<<grid, SCAN_CTA_THREADS, smem, stream>>>(a, per_cta, warm);
+            RRL_CUDA_OK(cudaGetLastError(), err);
+        } else {
+            // every descriptor word starts as the "unset" sentinel
+            RRL_CUDA_OK(cudaMemsetAsync(base, 0xFF, w.partials, stream), err);
+            const void *fn = with_baseline ? reinterpret_cast<const void *>(scan_kernel<true>)
+                                           : reinterpret_cast<const void *>(scan_kernel<false>);
+            RRL_TRY(occupancy(fn, wb));
+            // co-resident by construction: the look-back spins on tiles owned by other CTAs
+            const int grid = std::min(tiles, per_sm_cached[wb] * sms_cached);
+            void *args[] = {&a};
+            RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(SCAN_CTA_THREADS), args, smem, stream), err);
+        }
         if (launches) *launches += 1;
     }
     if (stats_out) {

@@ -97,7 +97,14 @@ SIGNATURES = {
     "rrl_normalise_device": (C.c_int32, [_P, C.c_int64, _P, _P, _P]),
 }
 
+DEV_SO_PATH = os.path.join(_HERE, "librelayrl_b200_dev.so")
 _lib = None
+
+
+def dev_lib():
+    """The developer library (tcgen05 self-test, rate probes, RRL_DISABLE_TC switch): tests/test_gpu_tc.py and tools/
+    only.  Loaded on its own handle; the product library is what everything else uses."""
+    return C.CDLL(DEV_SO_PATH)
 
 
 class RelayRLB200Error(RuntimeError):

@@ -272,3 +272,43 @@ def test_scan_special_values_take_the_slow_path(wb):
     got_a, got_r = run(rew2, val2)
     assert np.isnan(got_r[25000]) and np.isnan(got_a[25000])
     assert np.isfinite(got_r[39000:]).all()
+
+
+@pytest.mark.parametrize("gamma,lam", [(0.98, 0.97), (0.9995, 1.0), (1.0, 1.0), (0.5, 0.0)])
+@pytest.mark.parametrize("wb", [True, False])
+def test_scan_both_kernels_long_paths_vs_c_oracle(gamma, lam, wb):
+    """3 Mi transitions with paths of up to 1.2 Mi transitions (hundreds of tiles without a path end) through the
+    stateless operator.  gamma = 0.98 and 0.5 run the chunk kernel (every CTA recomputes the few tiles to its right
+    instead of waiting for them), gamma = 0.9995 and 1 -- whose influence never decays below the cut-off within a run --
+    the look-back kernel.  Both against the sequential float64 recurrence of oracle/scan_ref.c."""
+    import torch
+    from relayrl_b200 import scan_device, scan_workspace_bytes
+    rng = np.random.default_rng(int(gamma * 1e4) + int(wb))
+    n = 3 * 1024 * 1024 + 77
+    lens, tot = [], 0
+    while tot < n:
+        k = int(rng.integers(1, 500)) if rng.random() < 0.8 else int(rng.integers(100_000, 1_200_000))
+        k = min(k, n - tot)
+        lens.append(k)
+        tot += k
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    rew = (rng.uniform(-1, 1, n) * (1e-3 if gamma == 1.0 else 1.0)).astype(np.float32)
+    val = rng.standard_normal(n).astype(np.float32)
+    lvs = rng.uniform(-1, 1, len(lens)).astype(np.float32)
+    g, l = float(np.float32(gamma)), float(np.float32(lam))
+    dev = torch.device("cuda:0")
+    d = {k: torch.from_numpy(v).to(dev) for k, v in dict(rew=rew, val=val, offs=offs, lvs=lvs).items()}
+    adv, ret = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    stats = torch.zeros(8, dtype=torch.float64, device=dev)
+    ws = torch.empty(scan_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    scan_device(d["rew"], d["val"], d["offs"], d["lvs"], n, len(lens), g, l, wb, adv, ret, stats, ws,
+                stream=torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    a_ref, r_ref = sr.finish_paths(rew, val, offs, lvs, g, l, wb)
+    got_a, got_r = adv.cpu().numpy(), ret.cpu().numpy()
+    np.testing.assert_allclose(got_r, r_ref, rtol=RTOL, atol=ATOL * max(1.0, np.abs(r_ref).max() * 1e-3))
+    np.testing.assert_allclose(got_a, a_ref, rtol=RTOL, atol=ATOL * max(1.0, np.abs(a_ref).max() * 1e-3))
+    assert np.mean(got_a != a_ref) < 1e-3 and np.mean(got_r != r_ref) < 1e-3
+    s = stats.cpu().numpy()
+    np.testing.assert_allclose(s[0], got_a.astype(np.float64).sum(), rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(s[1], (got_a.astype(np.float64) ** 2).sum(), rtol=1e-9)

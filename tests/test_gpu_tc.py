@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 def test_tc_gemm_bf16x3(mode):
     import torch
     from relayrl_b200 import _lib
-    L = _lib.lib()
+    L = _lib.dev_lib()   # the self-test kernels are not part of the product library
     fn = L.rrl_debug_tc_gemm
     fn.restype, fn.argtypes = C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     rng = np.random.default_rng(mode)

@@ -2,6 +2,9 @@
 (per parameter block: W1,b1,W2,b2,W3,b3).  Usage: python tools/diag_grad_scale.py N [N ...]; RRL_DISABLE_TC=1 selects
 the CUDA-core kernel."""
 import os
+
+# RRL_DISABLE_TC is honoured by the developer library only
+os.environ.setdefault("RELAYRL_B200_SO", os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "relayrl-prototype_b200", "relayrl_b200", "librelayrl_b200_dev.so"))
 import sys
 
 import numpy as np

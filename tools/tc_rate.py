@@ -1,7 +1,7 @@
 import ctypes, sys, torch
 sys.path.insert(0, "/root/repo/relayrl-prototype_b200")
 from relayrl_b200 import _lib
-lib = _lib.lib()
+lib = _lib.dev_lib()
 f = lib.rrl_debug_tc_rate
 f.argtypes = [ctypes.c_int32] * 5 + [ctypes.c_void_p, ctypes.c_void_p]
 f.restype = ctypes.c_int32

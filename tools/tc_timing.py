@@ -3,7 +3,7 @@ os.environ["RELAYRL_B200_SO"] = "/root/repo/tools/_timing/librelayrl_b200_timing
 sys.path.insert(0, "/root/repo/relayrl-prototype_b200"); sys.path.insert(0, "/root/repo")
 import numpy as np, torch
 from relayrl_b200 import _lib
-lib = _lib.lib()
+lib = _lib.dev_lib()
 f = lib.rrl_debug_tc_timing
 f.argtypes = [ctypes.c_void_p, ctypes.c_int32]; f.restype = ctypes.c_int32
 import bench
