@@ -54,6 +54,7 @@ extern "C" {
 
 typedef struct rrl_learner rrl_learner_t;
 typedef struct rrl_actor rrl_actor_t;
+typedef struct rrl_rollout rrl_rollout_t;
 
 /* Constructor arguments of the reference algorithm class
  * (REINFORCE.__init__, src/native/python/algorithms/REINFORCE/REINFORCE.py:17-62) plus the
@@ -235,6 +236,22 @@ int32_t rrl_actor_step_device(rrl_actor_t *a, const float *obs, const float *mas
                               uint64_t seed, uint64_t offset, const int64_t *force_act,
                               int64_t *act, float *logp_a, float *v, float *probs, float *logits);
 const char *rrl_actor_last_error(const rrl_actor_t *a);
+
+/* ---- agent-side batched step service --------------------------------------------
+ * request_for_action / flag_last_action (src/network/client/agent_zmq.rs:458-571,605-610; agent_grpc.rs:372-455) for
+ * n_envs environments per call instead of one.  rrl_rollout_step runs the actor's batched step on host observations and
+ * stores, for every environment, the RelayRLAction the reference would build (obs, sampled act, mask, the reward passed
+ * with this call, data{logp_a, v}: agent_zmq.rs:536-552) as one packed row in device staging, environment-major, at
+ * most max_len rows per environment.  rrl_rollout_flag_last closes the listed environments' episodes: the terminal
+ * marker's reward becomes the path's last_val (REINFORCE.py:86) and the rows move into the learner's replay buffer
+ * device-to-device -- no safetensors blobs, no pickle, no host copy of the transitions.  Actor and learner must live on
+ * the same device with the same obs_dim / act_dim / baseline.  Calls on one rollout are serialised by the caller. */
+int32_t rrl_rollout_create(rrl_actor_t *actor, rrl_learner_t *learner, int64_t n_envs, int64_t max_len, rrl_rollout_t **out);
+int32_t rrl_rollout_destroy(rrl_rollout_t *r);
+int32_t rrl_rollout_step(rrl_rollout_t *r, const float *obs, const float *mask, const float *reward, uint64_t seed,
+                         uint64_t offset, int64_t *act, float *logp_a, float *v);
+int32_t rrl_rollout_flag_last(rrl_rollout_t *r, const int64_t *env_ids, const float *rewards, int64_t count);
+const char *rrl_rollout_last_error(const rrl_rollout_t *r);
 
 /* ---- stateless device operators (for callers that own their device memory) ----------------- */
 /* Scratch the scan needs for n transitions (tile descriptors for the single-pass look-back). */

@@ -89,6 +89,11 @@ SIGNATURES = {
     "rrl_actor_step_device": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_uint64, C.c_uint64, _P, _P, _P, _P,
                                           _P, _P]),
     "rrl_actor_last_error": (C.c_char_p, [_P]),
+    "rrl_rollout_create": (C.c_int32, [_P, _P, C.c_int64, C.c_int64, C.POINTER(_P)]),
+    "rrl_rollout_destroy": (C.c_int32, [_P]),
+    "rrl_rollout_step": (C.c_int32, [_P, _P, _P, _P, C.c_uint64, C.c_uint64, _P, _P, _P]),
+    "rrl_rollout_flag_last": (C.c_int32, [_P, _P, _P, C.c_int64]),
+    "rrl_rollout_last_error": (C.c_char_p, [_P]),
     "rrl_scan_workspace_bytes": (C.c_int32, [C.c_int64, C.POINTER(C.c_size_t)]),
     "rrl_scan_device": (C.c_int32, [_P, _P, _P, _P, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int32,
                                     _P, _P, _P, _P, C.c_size_t, _P]),
