@@ -50,6 +50,10 @@ extern "C" {
 #define RRL_LOGP_REFERENCE 0
 #define RRL_LOGP_LOG_SOFTMAX 1
 
+/* rrl_config_t.flags.  RRL_FLAG_TC_ANY_SIZE: run the tensor-core learner kernel at every batch size; by default batches
+ * under 32 768 transitions take the CUDA-core kernel (csrc/mlp_tc.cu, accuracy note).  For tests and diagnostics. */
+#define RRL_FLAG_TC_ANY_SIZE 1
+
 #define RRL_NCCL_ID_BYTES 128
 
 typedef struct rrl_learner rrl_learner_t;
@@ -70,7 +74,7 @@ typedef struct rrl_config {
     int32_t device;          /* CUDA ordinal */
     int32_t rank;            /* data-parallel rank; 0 when nranks == 1 */
     int32_t nranks;          /* 1 = single GPU */
-    int32_t reserved0;
+    int32_t flags;           /* RRL_FLAG_*; 0 by default */
     int64_t capacity;        /* buf_size, transitions */
     double gamma, lam;       /* replay_buffer.py:30 */
     double pi_lr, vf_lr;     /* REINFORCE.py:47,50 */

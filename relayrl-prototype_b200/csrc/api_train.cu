@@ -27,6 +27,7 @@ static TrainBuffers train_buffers(rrl_learner *h)
     TrainBuffers tb;
     tb.obs = h->obs, tb.act = h->act, tb.mask = h->mask, tb.adv = h->adv, tb.ret = h->ret, tb.logp_old = h->logp;
     tb.stats = h->stats, tb.n = h->ptr, tb.n_global = h->n_global;
+    tb.tc_any_size = (h->cfg.flags & RRL_FLAG_TC_ANY_SIZE) != 0;
     return tb;
 }
 

@@ -69,6 +69,7 @@ struct TrainBuffers {
     const double *stats;                                    // AdvStats (mean/std) for on-the-fly normalisation
     int64_t n;                                              // local transitions
     int64_t n_global;                                       // N over all ranks (the mean's denominator)
+    bool tc_any_size;                                       // RRL_FLAG_TC_ANY_SIZE
 };
 
 struct NetState {

@@ -596,7 +596,7 @@ int32_t run_pass(NetState &net, const TrainBuffers &tb, int mode, bool with_grad
 #else
     constexpr bool tc_off = false;
 #endif
-    if (!tc_off && tc_pass_supported(nd, mode, with_grad))
+    if (!tc_off && tc_pass_supported(nd, mode, with_grad, tb.tc_any_size ? (int64_t)1 << 40 : tb.n))
         st = tc_pass_launch(a, nd, mode, grid, stream, err);
     else if (mode == MODE_VALUE)
         st = launch_h<MODE_VALUE>(net, a, with_grad, grid, smem, stream, err);

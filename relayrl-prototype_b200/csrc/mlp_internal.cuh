@@ -29,7 +29,7 @@ struct MlpArgs {
 
 
 // mlp_tc.cu: tcgen05 path (hidden = 128, obs_dim <= 16, head width <= 4, reference logp mode)
-bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad);
+bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad, int64_t rows);
 size_t tc_smem_bytes();
 int32_t tc_pass_launch(const MlpArgs &a, const NetDims &nd, int mode, int grid, cudaStream_t stream, ErrBuf &err);
 

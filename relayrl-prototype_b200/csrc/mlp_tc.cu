@@ -42,6 +42,17 @@ constexpr uint32_t TM_D1 = 0, TM_P2 = 128, TM_D2 = 160, TM_DW2 = 224, TM_ACC = 3
 // f32 accumulation window of this kernel: 32 tiles = 2048 transitions, then the float64 spill (the CUDA-core kernel
 // uses 16; here a spill costs two barriers and 32 reductions per thread: 5.5 % of a tile at 16, 2.7 % at 32)
 constexpr int TC_FLUSH = 2 * FLUSH_TILES;
+// Accuracy note.  The tensor core adds each MMA into its fp32 accumulator by CHOPPING (toward zero), not rounding:
+// -4.3e-8 of |accumulator| per MMA on average (tools/tc_bias.py, profiles/r1_summary.md).  The small cross terms of the
+// bf16x3 product are issued first, so what matters are the K/16 main MMAs at the end.  When the terms of a sum share a sign
+// the result comes out up to ~2e-7 (relative) short -- within float32 rounding of any single number, but SYSTEMATIC.  On
+// C1-sized batches (~2500 transitions) late in training, where the value targets are large and the residuals small, that
+// made every v about 2e-7 too small and the value-head bias gradient 1.1e-5 short; Adam normalises gradients, and a
+// quarter of the weights drifted by up to 1.8 lr per epoch against the float64 run (tools/diag_c1_grad.py, measured).
+// A constant correction factor was tried and rejected: for sums whose terms cancel (fresh weights) there is no such bias
+// and the factor then costs the golden epoch its 1e-5 agreement.  Hence TC_MIN_ROWS: batches too small to fill the
+// pipeline anyway (where the effect is visible) take the CUDA-core kernel, whose float32 FMAs round to nearest.
+constexpr int64_t TC_MIN_ROWS = 32768;  // ~3.5 tiles per SM; below it the CUDA-core kernel runs (see the note above)
 constexpr int NBUF = 4;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1), k+2 (in flight)
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
@@ -649,9 +660,9 @@ extern "C" int32_t rrl_debug_tc_timing(unsigned long long *out16, int32_t reset)
 }
 #endif
 
-bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad)
+bool tc_pass_supported(const NetDims &nd, int mode, bool with_grad, int64_t rows)
 {
-    return with_grad && nd.H == TC_H && nd.d <= TC_MAX_D && nd.out <= TC_MAX_OUT && (mode == MODE_VALUE || mode == MODE_POLICY_REF);
+    return rows >= TC_MIN_ROWS && with_grad && nd.H == TC_H && nd.d <= TC_MAX_D && nd.out <= TC_MAX_OUT && (mode == MODE_VALUE || mode == MODE_POLICY_REF);
 }
 
 size_t tc_smem_bytes() { return TC_SMEM_BYTES; }

@@ -80,6 +80,11 @@ __device__ __forceinline__ void st_stream4(float *p, float a, float b, float c, 
 // 9.8 for the integer-ALU widening the round-1 kernel used (7 instructions + the select for zero).  At five conversions
 // per transition that is 0.07 ms of the XU pipe for 64 Mi transitions, in parallel with the FP64 pipe and the loads.
 __device__ __forceinline__ double widen(float x) { return (double)x; }
+// acc += m * x where p holds: one predicated DFMA (the compiler's own choice is an unconditional DFMA + two FSELs)
+__device__ __forceinline__ void fma_if(double &acc, double m, double x, bool p)
+{
+    asm("{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %3, 0;\n\t@q fma.rn.f64 %0, %1, %2, %0;\n\t}" : "+d"(acc) : "d"(m), "d"(x), "r"((int)p));
+}
 __device__ __forceinline__ float narrow(double x) { return __double2float_rn(x); }
 
 struct ScanArgs {
@@ -127,7 +132,10 @@ struct ScanCtl {  // consumer hand-offs inside one tile
     double2 chain[2];              // chunk mode: (ret, adv) at the first element of the tile this CTA did last (by parity)
     double2 tpow[32];              // tp^i (ret, adv), i = 0..31: the look-back's per-lane slopes (set once per CTA)
 };
-constexpr double SCAN_CUT = 1e-100;
+// Slope below which a carry is dropped.  The carried value is at most max|x| / (1 - c) (<= 1e5 max|x| up to c = 0.99999),
+// so what is dropped is below 1e-25 of the largest input: nine decades under the rounding error the float64 recurrence
+// itself commits on every sum (1e-16 of its terms), i.e. invisible even to the float64 oracle, let alone after f32 rounding.
+constexpr double SCAN_CUT = 1e-30;
 constexpr double SCAN_CUT_HOST = SCAN_CUT;
 
 #ifdef SCAN_TIMING  // developer build only: clock64 spans of CTA 0 (warp 1 of the consumers, lane 0; the producer's lane 0)
@@ -285,7 +293,8 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
 // value at its first element is wanted (no outputs, no statistics).
 template <bool WB, bool CHUNK>
 __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int tile, int64_t n_scan, int num_tiles,
-                                             ScanCtl &S, int tid, double lane_r, double lane_a, int parity, bool warm)
+                                             ScanCtl &S, int tid, double lane_r, double lane_a, int parity, bool warm,
+                                             double &acc1, double &acc2)
 {
     const int lane = tid & 31, warp = tid >> 5;
     SCT_DECL;
@@ -368,7 +377,8 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
     for (int s = 0; s < 5; ++s) {
         const int d = 1 << s;
         const double o_r = __shfl_down_sync(0xffffffffu, sr, d), o_a = __shfl_down_sync(0xffffffffu, sa, d);
-        if (lane + d < 32 && dist >= d) sr = fma(a.st_r[s], o_r, sr), sa = fma(a.st_a[s], o_a, sa);
+        const bool on = lane + d < 32 && dist >= d;
+        fma_if(sr, a.st_r[s], o_r, on), fma_if(sa, a.st_a[s], o_a, on);
     }
     double er = __shfl_down_sync(0xffffffffu, sr, 1), ea = __shfl_down_sync(0xffffffffu, sa, 1);  // the lanes to the right
     if (lane == 31) er = 0.0, ea = 0.0;
@@ -381,7 +391,18 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
     // ---- the eight warps; look-back kernel: warp 0 alone, with the tile's descriptor and the look-back; chunk kernel:
     // every warp for itself (a dozen instructions), which saves the second barrier and the wait for warp 0 -------------
     double wc_r = 0.0, wc_a = 0.0;  // the carry that enters this warp from the right
-    if (CHUNK || warp == 0) {
+    if (CHUNK) {
+        // every warp walks the (at most seven) warps to its right, starting from the carry the previous tile left
+        const double2 prev = S.chain[parity ^ 1];
+        if (open_right) wc_r = prev.x, wc_a = prev.y;
+        for (int w2 = SCAN_WARPS - 1; w2 > warp; --w2) {
+            const double2 g = S.wagg[w2];
+            const bool cl = S.wclosed[w2] != 0u;
+            wc_r = cl ? g.x : fma(a.wp_r, wc_r, g.x), wc_a = cl ? g.y : fma(a.wp_a, wc_a, g.y);
+        }
+        if (warp == 0 && lane == 0)  // the value at this tile's first element: the next tile's carry
+            S.chain[parity] = em ? make_double2(sr, sa) : make_double2(fma(a.wp_r, wc_r, sr), fma(a.wp_a, wc_a, sa));
+    } else if (warp == 0) {
         double xr = 0.0, xa = 0.0;
         if (lane < SCAN_WARPS) xr = S.wagg[lane].x, xa = S.wagg[lane].y;
         const unsigned cm = __ballot_sync(0xffffffffu, lane < SCAN_WARPS && S.wclosed[lane] != 0u);  // warps with a path end
@@ -396,19 +417,13 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
         // lane 0: the whole tile
         const bool closed = cm != 0u;  // the value at the tile's first element does not depend on the carry-in
-        if (!CHUNK && lane == 0) {
+        if (lane == 0) {
             if (closed)
                 st_relaxed2(&a.incl[tile], xr, xa);
             else
                 st_relaxed2(&a.agg[tile], xr, xa);
         }
         double cr = 0.0, ca = 0.0;  // carry into the tile from the tiles to the right
-        if (CHUNK) {
-            const double2 prev = S.chain[parity ^ 1];  // the tile just done by this CTA: the value at its first element
-            if (open_right) cr = prev.x, ca = prev.y;
-            if (warp == 0 && lane == 0)
-                S.chain[parity] = closed ? make_double2(xr, xa) : make_double2(fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
-        } else
 #ifdef SCAN_DBG_NO_LOOKBACK  // timing experiment only (wrong results)
         if (false) {
 #else
@@ -421,11 +436,10 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 const int k = base + lane;
                 double qr = 0.0, qa = 0.0;
                 bool final_value = true;  // beyond the last tile there is nothing to carry
-                // A tile whose slope towards this one has fallen below SCAN_CUT cannot change any f32 output: its
-                // value (<= 3.4e38 / (1 - c) for finite f32 inputs) times the slope is below 1e-56, eleven decades
-                // under the smallest f32 denormal.  Such lanes are not polled and end the look-back: with gamma = 0.98
-                // (tp = 1e-18) six tiles are read instead of every tile in flight to the right (up to ~440: the
-                // CTAs move in step, so their inclusive values appear together, late).
+                // A tile whose slope towards this one has fallen below SCAN_CUT (see there) cannot change the result.
+                // Such lanes are not polled and end the look-back: with gamma = 0.98 (tp = 1e-18) two tiles are read
+                // instead of every tile in flight to the right (up to ~440: the CTAs move in step, so their inclusive
+                // values appear together, late).
                 const bool needed = fmax(sc_r * lt_r, sc_a * lt_a) >= SCAN_CUT;
                 if (k < num_tiles && needed) {
                     while (true) {
@@ -455,7 +469,7 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 base += 32;
             }
         }
-        if (!CHUNK && lane == 0 && !closed) st_relaxed2(&a.incl[tile], fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
+        if (lane == 0 && !closed) st_relaxed2(&a.incl[tile], fma(a.tp_r, cr, xr), fma(a.tp_a, ca, xa));
         // carry into warp w: the warps to its right for a zero tile carry, plus the tile carry across them when open
         double nr = __shfl_down_sync(0xffffffffu, xr, 1), na = __shfl_down_sync(0xffffffffu, xa, 1);
         if (lane < SCAN_WARPS) {
@@ -465,9 +479,8 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
                 for (int i = lane; i < SCAN_WARPS - 1; ++i) qr *= a.wp_r, qa *= a.wp_a;
                 nr = fma(qr, cr, nr), na = fma(qa, ca, na);
             }
-            if (!CHUNK) S.wcarry[lane] = make_double2(nr, na);
+            S.wcarry[lane] = make_double2(nr, na);
         }
-        if (CHUNK) wc_r = __shfl_sync(0xffffffffu, nr, warp), wc_a = __shfl_sync(0xffffffffu, na, warp);
     }
     if (!CHUNK) consumer_sync();
     SCT(3, sct_me);  // warp 0's combine + look-back (as seen by a waiting warp)
@@ -522,6 +535,10 @@ __device__ __forceinline__ void scan_consume(const ScanArgs &a, TileBuf &B, int 
         }
     }
     SCT(7, sct_me);  // pass 2: stores
+    if (CHUNK) {  // the CTA's tiles are its own: the sums ride in registers until its run ends
+        acc1 += s1, acc2 += s2;
+        return;
+    }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         s1 += __shfl_xor_sync(0xffffffffu, s1, d);
@@ -562,6 +579,7 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
     if (producer) scan_prepare<WB>(a, buf[0], n_scan, num_tiles, lane, j);
     __syncthreads();
     int b = 0, prev_tile = -1;
+    double unused1 = 0.0, unused2 = 0.0;
     while (true) {
         const int tile = buf[b].tile;
         // the previous tile's statistics: its eight warp sums in a fixed order (the result does not depend on which
@@ -576,7 +594,7 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
         if (producer)
             scan_prepare<WB>(a, buf[b ^ 1], n_scan, num_tiles, lane, j);
         else
-            scan_consume<WB, false>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, false);
+            scan_consume<WB, false>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, false, unused1, unused2);
         SCT_DECL;
         __syncthreads();
         SCT(5, tid == 32);                // consumers waiting for the producer
@@ -593,9 +611,9 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_kernel(S
 // Chunk mode: CTA c owns the contiguous logical tiles [c K, (c + 1) K) and walks them right-to-left, so the carry
 // from tile to tile never leaves the CTA.  What comes in from the CTA's right-hand neighbour is recomputed instead of
 // waited for: the CTA first runs `warm` extra tiles to the right of its run through pass 1 only.  After W open tiles the
-// influence of anything further right is slope^W < SCAN_CUT (see the look-back cut-off: below 1e-56 in absolute terms,
-// eleven decades under the smallest f32 denormal), and a path end inside the warm-up makes it exact.  For gamma = 0.98
-// that is 6 tiles of reads for every ~74 tiles of work, no descriptors, no polling, no memset, no co-residency.  The
+// influence of anything further right is slope^W < SCAN_CUT (below the float64 recurrence's own rounding, see SCAN_CUT),
+// and a path end inside the warm-up makes it exact.  For gamma = 0.98
+// that is 2 tiles of reads for every ~74 tiles of work, no descriptors, no polling, no memset, no co-residency.  The
 // look-back kernel above stays for discounts so close to 1 that the warm-up would outgrow the run (scan_launch picks).
 template <bool WB>
 __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_chunk_kernel(ScanArgs a, int tiles_per_cta, int warm)
@@ -622,24 +640,36 @@ __global__ void __launch_bounds__(SCAN_CTA_THREADS, SCAN_MIN_CTAS) scan_chunk_ke
 
     if (producer) scan_prepare<WB>(a, buf[0], n_scan, j < j_end ? num_tiles : 0, lane, j, &ps);
     __syncthreads();
-    int b = 0, prev_tile = -1;
+    int b = 0;
+    double acc1 = 0.0, acc2 = 0.0;  // this thread's (sum, sum of squares) of the f32-rounded advantages over the run
     while (true) {
         const int tile = buf[b].tile;
-        if (tid == 0 && prev_tile >= 0) {  // the previous tile's statistics, eight warp sums in a fixed order
-            double t1 = 0.0, t2 = 0.0;
-            for (int w = 0; w < SCAN_WARPS; ++w) t1 += ctl.wstat[b ^ 1][w].x, t2 += ctl.wstat[b ^ 1][w].y;
-            a.partials[prev_tile] = make_double2(t1, t2);
-        }
         if (tile < 0) break;
         const bool is_warm = j < j_begin;
         ++j;
         if (producer)
             scan_prepare<WB>(a, buf[b ^ 1], n_scan, j < j_end ? num_tiles : 0, lane, j, &ps);
         else
-            scan_consume<WB, true>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, is_warm);
+            scan_consume<WB, true>(a, buf[b], tile, n_scan, num_tiles, ctl, tid, lane_r, lane_a, b, is_warm, acc1, acc2);
         __syncthreads();
-        prev_tile = is_warm ? -1 : tile;
         b ^= 1;
+    }
+    // the run's statistics, reduced once in a fixed order (the tile -> CTA map is static, so the result is reproducible):
+    // the CTA's first tile carries the total, its other tiles zero (stats_reduce_kernel sums per-tile entries)
+    if (!producer) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            acc1 += __shfl_xor_sync(0xffffffffu, acc1, d);
+            acc2 += __shfl_xor_sync(0xffffffffu, acc2, d);
+        }
+        if (lane == 0) ctl.wstat[0][tid >> 5] = make_double2(acc1, acc2);
+    }
+    __syncthreads();
+    for (int jj = j_begin + tid; jj < j_end; jj += SCAN_CTA_THREADS) {
+        double2 t = make_double2(0.0, 0.0);
+        if (jj == j_begin)
+            for (int w = 0; w < SCAN_WARPS; ++w) t.x += ctl.wstat[0][w].x, t.y += ctl.wstat[0][w].y;
+        a.partials[num_tiles - 1 - jj] = t;
     }
 }
 

@@ -7,7 +7,7 @@ use std::ffi::{c_char, c_void, CStr};
 #[repr(C)]
 pub struct RrlConfig {
     pub obs_dim: i32, pub act_dim: i32, pub hidden: i32, pub with_baseline: i32, pub train_vf_iters: i32,
-    pub logp_mode: i32, pub device: i32, pub rank: i32, pub nranks: i32, pub reserved0: i32,
+    pub logp_mode: i32, pub device: i32, pub rank: i32, pub nranks: i32, pub flags: i32,
     pub capacity: i64, pub gamma: f64, pub lam: f64, pub pi_lr: f64, pub vf_lr: f64,
     pub adam_beta1: f64, pub adam_beta2: f64, pub adam_eps: f64, pub nccl_id: [u8; 128],
 }

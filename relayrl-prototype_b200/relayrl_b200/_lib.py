@@ -13,13 +13,14 @@ SO_PATH = os.environ.get("RELAYRL_B200_SO") or os.path.join(_HERE, "librelayrl_b
 RRL_OK = 0
 RRL_F32, RRL_F64 = 0, 1
 RRL_LOGP_REFERENCE, RRL_LOGP_LOG_SOFTMAX = 0, 1
+RRL_FLAG_TC_ANY_SIZE = 1
 NCCL_ID_BYTES = 128
 
 
 class Config(C.Structure):
     _fields_ = [("obs_dim", C.c_int32), ("act_dim", C.c_int32), ("hidden", C.c_int32),
                 ("with_baseline", C.c_int32), ("train_vf_iters", C.c_int32), ("logp_mode", C.c_int32),
-                ("device", C.c_int32), ("rank", C.c_int32), ("nranks", C.c_int32), ("reserved0", C.c_int32),
+                ("device", C.c_int32), ("rank", C.c_int32), ("nranks", C.c_int32), ("flags", C.c_int32),
                 ("capacity", C.c_int64), ("gamma", C.c_double), ("lam", C.c_double),
                 ("pi_lr", C.c_double), ("vf_lr", C.c_double), ("adam_beta1", C.c_double),
                 ("adam_beta2", C.c_double), ("adam_eps", C.c_double),

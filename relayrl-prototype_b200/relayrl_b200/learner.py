@@ -36,13 +36,13 @@ def _dev_ptr(t):
 class Learner:
     def __init__(self, obs_dim, act_dim, capacity, hidden=128, with_baseline=True, gamma=0.98, lam=0.97,
                  pi_lr=3e-4, vf_lr=1e-3, train_vf_iters=80, device=0, logp_mode=_lib.RRL_LOGP_REFERENCE,
-                 rank=0, nranks=1, nccl_id=None):
+                 rank=0, nranks=1, nccl_id=None, flags=0):
         self._L = _lib.lib()
         cfg = Config()
         self._L.rrl_config_defaults(C.byref(cfg))
         cfg.obs_dim, cfg.act_dim, cfg.hidden = obs_dim, act_dim, hidden
         cfg.with_baseline, cfg.train_vf_iters, cfg.logp_mode = int(with_baseline), train_vf_iters, logp_mode
-        cfg.device, cfg.rank, cfg.nranks, cfg.capacity = device, rank, nranks, capacity
+        cfg.device, cfg.rank, cfg.nranks, cfg.capacity, cfg.flags = device, rank, nranks, capacity, flags
         cfg.gamma, cfg.lam, cfg.pi_lr, cfg.vf_lr = f32(gamma), f32(lam), f32(pi_lr), f32(vf_lr)
         if nranks > 1:
             assert nccl_id is not None and len(nccl_id) == _lib.NCCL_ID_BYTES

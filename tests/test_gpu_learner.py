@@ -24,8 +24,11 @@ def assert_weights_close(actual, desired, lr, learner=None, which=None, excused=
     lr * m_hat / (sqrt(v_hat) + eps) stops being scale-invariant where sqrt(v_hat) ~ eps = 1e-8, so there a 1e-7 relative
     wobble of the gradient (float32 summation order) moves the weight by a visible fraction of lr.  Measured on B200
     (tools/diag_outliers.py, golden epochs): 0-2 such parameters of 17 k, sqrt(v_hat) between 3e-10 and 5e-8 against a
-    largest sqrt(v_hat) of 2e-2 .. 9e-2, error <= 0.009 lr.  With `learner` given, a NEW outlier must have
-    sqrt(v_hat) < 1e-5 of the largest; `excused` carries outliers of earlier epochs (the error stays, v_hat grows)."""
+    largest sqrt(v_hat) of 2e-2 .. 9e-2, error <= 0.009 lr; the CUDA-core kernel: one weight at sqrt(v_hat) = 9.7e-5,
+    error 0.0008 lr after 80 steps.  With `learner` given, a NEW outlier must be explained by its conditioning: float32
+    summation noise of 3e-7 of the largest gradient entry per step moves a weight by at most
+    lr * 3e-7 * max sqrt(v_hat) / sqrt(v_hat_i) per step, 80 steps an epoch; `excused` carries outliers of earlier
+    epochs (the error stays, v_hat grows)."""
     actual, desired = np.asarray(actual), np.asarray(desired)
     err = np.abs(actual - desired)
     out = set(np.flatnonzero(err > W_ATOL + W_RTOL * np.abs(desired)).tolist())
@@ -41,8 +44,9 @@ def assert_weights_close(actual, desired, lr, learner=None, which=None, excused=
         m, v, step = learner.get_opt_state(which)
         sv = np.sqrt(v / (1.0 - 0.999 ** step))
         for i in sorted(out - (excused or set())):
-            assert sv[i] < 1e-5 * sv.max(), "parameter %d misses the bound with a healthy sqrt(v_hat) = %.3g (max %.3g)" % (
-                i, sv[i], sv.max())
+            bound = 80 * 3e-7 * sv.max() / max(sv[i], 1e-8)
+            assert err[i] / lr <= bound, "parameter %d is off by %.3g lr with sqrt(v_hat) = %.3g (max %.3g): more than its " \
+                "conditioning explains (%.3g lr)" % (i, err[i] / lr, sv[i], sv.max(), bound)
     return out | (excused or set())
 
 
@@ -344,7 +348,7 @@ def test_tc_gradients_many_tiles_vs_float64_autograd(n, d, A):
     O = lo.OracleLearner(d, A, m + 1, hidden=H, with_baseline=True, train_vf_iters=1, seed=5)
     pi0, v0 = [p.detach().clone() for p in O.pi], [p.detach().clone() for p in O.v]
     from relayrl_b200 import Learner
-    L = Learner(d, A, m + 1, hidden=H, with_baseline=True, train_vf_iters=1)
+    L = Learner(d, A, m + 1, hidden=H, with_baseline=True, train_vf_iters=1, flags=1)   # the tensor-core kernel at any size
     L.set_params(0, lo.flatten(pi0).numpy())
     L.set_params(1, lo.flatten(v0).numpy())
     O.ingest(obs, act, mask, rew, val, logp, done)
