@@ -356,12 +356,16 @@ def measure_without_baseline(dev, local, n=1 << 20, reps=5):
             "cpu_transitions_per_s": n / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
 
 
-def correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world):
-    """Outside every timed region: the result of the path the bench just timed, checked on the spot.
+def correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world, final=True):
+    """Outside every timed region: the result of the path the bench times, checked on the spot -- once at the initial
+    weights (final=False) and once after the timed steps.
     (1) value and policy loss and the value gradient at the CURRENT weights, from the library (rrl_eval_grad: the same
         kernels as a training step, gradient all-reduced over the ranks) against a float64 evaluation of the same device
-        buffers by plain torch (tests/f64_eval.py; sums all-reduced over the ranks): rel 1e-5 on the losses, 3e-5 in the
-        L2 norm on the gradient (tests/test_gpu_scale.py explains the bound);
+        buffers by plain torch (tests/f64_eval.py; sums all-reduced over the ranks): rel 1e-5 on the losses, always; 3e-5 in
+        the L2 norm on the gradient (tests/test_gpu_scale.py explains the bound) at the initial weights.  After the timed
+        steps the synthetic targets (noise) are fitted as far as they can be: the per-row terms of the gradient cancel to
+        ~1e-4 of their size, so its relative error is float32 row noise times that amplification (measured 4e-4 .. 2e-3
+        on one and on two GPUs alike, csrc/mlp_tc.cu "Accuracy note") -- reported, not asserted;
     (2) at N > 1: every rank holds bit-identical weights after the timed steps (same all-reduced float64 gradient, same
         Adam) -- the data-parallel replicas never need a broadcast.
     A failure raises: a SCALE run that diverged does not print a line."""
@@ -370,7 +374,7 @@ def correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world):
     import f64_eval
     pi, vf = L.get_params(0), L.get_params(1)
     out = {}
-    if world > 1:
+    if world > 1 and final:
         mine = torch.from_numpy(np.concatenate([pi, vf])).to(dev)
         ref = mine.clone()
         dist.broadcast(ref, 0)
@@ -395,9 +399,15 @@ def correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world):
     g64 = g64.cpu().numpy()
     out.update(loss_v=got[1], loss_v_float64=want[1], loss_pi=got[0], loss_pi_float64=want[0],
                value_grad_rel_l2=float(np.linalg.norm(gv - g64) / np.linalg.norm(g64)))
+    blocks, o = {}, 0
+    for name, k in (("W1", H * D), ("b1", H), ("W2", H * H), ("b2", H), ("W3", H), ("b3", 1)):
+        blocks[name] = float(np.linalg.norm(gv[o:o + k] - g64[o:o + k]) / max(np.linalg.norm(g64[o:o + k]), 1e-300))
+        o += k
+    out["value_grad_rel_l2_by_block"] = blocks
     assert abs(got[1] - want[1]) <= 1e-5 * abs(want[1]), out
     assert abs(got[0] - want[0]) <= 1e-5 * abs(want[0]) + 1e-7, out
-    assert out["value_grad_rel_l2"] <= 3e-5, out
+    if not final:
+        assert out["value_grad_rel_l2"] <= 3e-5, out
     out["passed"] = True
     return out
 
@@ -536,6 +546,7 @@ def run_ours(args):
             dt = t.item()
         return dt, stats
 
+    check0 = None if args.no_check else correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world, final=False)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -543,7 +554,8 @@ def run_ours(args):
     clocks = sampler.finish() if rank == 0 else None
     dt_e2e, stats_e2e = timed(step_e2e, args.steps, 1)   # the same number of timed steps as `value`
     e2e_steps = args.steps
-    check = None if args.no_check else correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world)
+    check = None if args.no_check else {"initial_weights": check0,
+                                        "after_timed_steps": correctness_check(L, cols, offsets, last_vals, n, dev, dist, rank, world)}
 
     scan_ms = measure_scan(cols, offsets, last_vals, n, dev)
     extras = {}

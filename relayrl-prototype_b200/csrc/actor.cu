@@ -9,7 +9,7 @@
 // sample -> (value net) -> outputs.  Activations stay in shared memory; weights stream from L2
 // through a double-buffered cp.async ring in 32-wide K chunks, so any hidden size that is a
 // multiple of 32 up to 256 fits.  fp32 CUDA-core math (parity: rel 1e-5 vs the torch CPU oracle).
-#include "common.cuh"
+#include "actor_internal.cuh"
 
 namespace rrl {
 
@@ -21,22 +21,6 @@ constexpr int ACT_KC = 32;   // K chunk
 constexpr int ACT_LDB = ACT_KC + 4;
 constexpr int ACT_MAX_OUT = 32;
 
-struct ActorNet {
-    const float *params;  // flat torch order
-    const float *w1p;     // W1 padded to [H][dK] (dK = roundup(d, 4)), zero filled
-};
-
-struct ActorArgs {
-    ActorNet pi, vf;
-    int d, dK, A, with_v;
-    const float *obs, *mask;
-    int64_t batch;
-    uint64_t seed, offset;
-    const int64_t *force_act;
-    int64_t *act;
-    float *logp_a, *v, *probs, *logits;
-};
-
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src, int src_bytes)
 {
     const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -47,22 +31,6 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait()
 {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
-// Philox4x32-10 (Salmon et al. 2011), counter = (ctr, 0), key = seed; returns the first word.
-__device__ __forceinline__ unsigned philox_first(uint64_t seed, uint64_t ctr)
-{
-    unsigned c0 = (unsigned)ctr, c1 = (unsigned)(ctr >> 32), c2 = 0u, c3 = 0u;
-    unsigned k0 = (unsigned)seed, k1 = (unsigned)(seed >> 32);
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const unsigned hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const unsigned hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        const unsigned n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
-        c0 = n0, c1 = n1, c2 = n2, c3 = n3;
-        k0 += 0x9E3779B9u, k1 += 0xBB67AE85u;
-    }
-    return c0;
 }
 
 // out_s[m][n] = relu?(bias[n] + sum_k A_s[m][k] * W[n][k]),  W row-major [H][ldw] in global memory
@@ -199,42 +167,9 @@ __global__ void __launch_bounds__(ACT_THREADS, 1) actor_kernel(ActorArgs a)
 
     // ---- softmax, sample, gather (kernel.py:23-37) -----------------------------------------------
     if (tid < rows) {
-        const int m = tid;
-        const int64_t row = row0 + m;
-        float mx = -INFINITY;
-        for (int q = 0; q < A; ++q) {
-            const float lg = head_s[m * A + q] + (__ldcs(a.mask + row * A + q) - 1.f) * 1e8f;
-            head_s[m * A + q] = lg;
-            mx = fmaxf(mx, lg);
-        }
-        float se = 0.f;
-        for (int q = 0; q < A; ++q) se += expf(head_s[m * A + q] - mx);
-        int at;
-        if (a.force_act) {
-            at = (int)a.force_act[row];
-            at = min(max(at, 0), A - 1);
-        } else {
-            // inverse CDF with one Philox uniform in [0,1); a masked action has p == 0 exactly
-            const float u = (float)(philox_first(a.seed, a.offset + (uint64_t)row) >> 8) * (1.0f / 16777216.0f);
-            float c = 0.f;
-            at = -1;
-            int last_pos = 0;
-            for (int q = 0; q < A; ++q) {
-                const float p = expf(head_s[m * A + q] - mx) / se;
-                if (p > 0.f) last_pos = q;
-                c += p;
-                if (at < 0 && u < c) at = q;
-            }
-            if (at < 0) at = last_pos;
-        }
-        for (int q = 0; q < A; ++q) {
-            const float lg = head_s[m * A + q];
-            if (a.logits) a.logits[row * A + q] = lg;
-            if (a.probs) a.probs[row * A + q] = expf(lg - mx) / se;
-        }
-        a.act[row] = at;
-        a.logp_a[row] = head_s[m * A + at];  // raw masked logit
-        if (a.with_v && a.v) a.v[row] = vhead_s[m];
+        const int64_t row = row0 + tid;
+        actor_policy_tail(a, head_s + tid * A, 1, row);
+        if (a.with_v && a.v) a.v[row] = vhead_s[tid];
     }
 }
 
@@ -281,7 +216,7 @@ int32_t actor_pad_w1_launch(const float *params, int H, int d, float *w1p, cudaS
 }
 
 int32_t actor_forward_launch(const float *pi_params, const float *pi_w1p, const float *vf_params,
-                             const float *vf_w1p, int d, int H, int A, const float *obs, const float *mask,
+                             const float *vf_w1p, const unsigned char *pi_pack, const unsigned char *vf_pack, int d, int H, int A, const float *obs, const float *mask,
                              int64_t batch, uint64_t seed, uint64_t offset, const int64_t *force_act, int64_t *act,
                              float *logp_a, float *v, float *probs, float *logits, cudaStream_t stream, ErrBuf &err)
 {
@@ -289,9 +224,12 @@ int32_t actor_forward_launch(const float *pi_params, const float *pi_w1p, const 
     RRL_TRY(actor_check_dims(d, H, A, err));
     ActorArgs a;
     a.pi.params = pi_params, a.pi.w1p = pi_w1p, a.vf.params = vf_params, a.vf.w1p = vf_w1p;
+    a.pi.pack = pi_pack, a.vf.pack = vf_pack;
     a.d = d, a.dK = (d + 3) & ~3, a.A = A, a.with_v = vf_params != nullptr;
     a.obs = obs, a.mask = mask, a.batch = batch, a.seed = seed, a.offset = offset, a.force_act = force_act;
     a.act = act, a.logp_a = logp_a, a.v = v, a.probs = probs, a.logits = logits;
+    // wide layers and enough environments to fill 128-row tiles: the tensor-core kernel (actor_tc.cu)
+    if (pi_pack && (!vf_params || vf_pack) && actor_tc_supported(d, H, A, batch)) return actor_tc_forward_launch(a, H, stream, err);
     const size_t smem = actor_smem_bytes(d, H);
     const int grid = (int)((batch + ACT_TM - 1) / ACT_TM);
 #define RRL_ACTOR_CASE(HH)                                                                                            \

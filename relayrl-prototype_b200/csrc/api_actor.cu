@@ -19,6 +19,7 @@ int32_t rrl_actor_destroy(rrl_actor_t *a)
     cudaSetDevice(a->device);
     if (a->stream) cudaStreamSynchronize(a->stream);
     cudaFree(a->pi_params), cudaFree(a->pi_w1p), cudaFree(a->vf_params), cudaFree(a->vf_w1p);
+    cudaFree(a->pi_pack), cudaFree(a->vf_pack);
     cudaFree(a->d_obs), cudaFree(a->d_mask), cudaFree(a->d_logp), cudaFree(a->d_v), cudaFree(a->d_probs);
     cudaFree(a->d_logits), cudaFree(a->d_act);
     if (a->order_ev) cudaEventDestroy(a->order_ev);
@@ -58,6 +59,10 @@ int32_t rrl_actor_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32
     };
     al((void **)&a->pi_params, pd.n_params() * 4), al((void **)&a->pi_w1p, hidden * dK * 4);
     if (with_baseline) al((void **)&a->vf_params, vd.n_params() * 4), al((void **)&a->vf_w1p, hidden * dK * 4);
+    if (const size_t pk = actor_pack_bytes(obs_dim, hidden)) {
+        al((void **)&a->pi_pack, pk);
+        if (with_baseline) al((void **)&a->vf_pack, pk);
+    }
     al((void **)&a->d_obs, B * obs_dim * 4), al((void **)&a->d_mask, B * act_dim * 4), al((void **)&a->d_logp, B * 4);
     al((void **)&a->d_v, B * 4), al((void **)&a->d_probs, B * act_dim * 4), al((void **)&a->d_logits, B * act_dim * 4);
     al((void **)&a->d_act, B * 8);
@@ -85,6 +90,8 @@ int32_t rrl_actor_set_params(rrl_actor_t *a, int32_t which, const float *flat, i
     float *dst = which == 0 ? a->pi_params : a->vf_params, *w1p = which == 0 ? a->pi_w1p : a->vf_w1p;
     RRL_CUDA_OK(cudaMemcpyAsync(dst, flat, n * 4, cudaMemcpyHostToDevice, a->stream), a->err);
     RRL_TRY(actor_pad_w1_launch(dst, a->H, a->d, w1p, a->stream, a->err));
+    if (unsigned char *pack = which == 0 ? a->pi_pack : a->vf_pack)
+        RRL_TRY(actor_pack_launch(dst, a->d, a->H, nd.out, pack, a->stream, a->err));
     RRL_CUDA_OK(cudaStreamSynchronize(a->stream), a->err);
     return RRL_OK;
 }
@@ -99,7 +106,7 @@ int32_t rrl_actor_step_device(rrl_actor_t *a, const float *obs, const float *mas
         return RRL_EINVAL;
     }
     if (a->order_ev) RRL_CUDA_OK(order_after_default_stream(a->stream, a->order_ev), a->err);  // inputs made on stream 0
-    RRL_TRY(actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->d,
+    RRL_TRY(actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->pi_pack, a->vf_pack, a->d,
                                  a->H, a->A, obs, mask, batch, seed, offset, force_act, act, logp_a, v, probs, logits,
                                  a->stream, a->err));
     RRL_CUDA_OK(cudaStreamSynchronize(a->stream), a->err);  // outputs are complete when the call returns
@@ -119,7 +126,7 @@ int32_t rrl_actor_step(rrl_actor_t *a, const float *obs, const float *mask, int6
     const size_t B = (size_t)batch;
     RRL_CUDA_OK(cudaMemcpyAsync(a->d_obs, obs, B * a->d * 4, cudaMemcpyHostToDevice, st), a->err);
     RRL_CUDA_OK(cudaMemcpyAsync(a->d_mask, mask, B * a->A * 4, cudaMemcpyHostToDevice, st), a->err);
-    RRL_TRY(actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->d,
+    RRL_TRY(actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->pi_pack, a->vf_pack, a->d,
                                  a->H, a->A, a->d_obs, a->d_mask, batch, seed, offset, nullptr, a->d_act, a->d_logp,
                                  a->d_v, probs ? a->d_probs : nullptr, logits ? a->d_logits : nullptr, st, a->err));
     RRL_CUDA_OK(cudaMemcpyAsync(act, a->d_act, B * 8, cudaMemcpyDeviceToHost, st), a->err);

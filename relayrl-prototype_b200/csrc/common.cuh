@@ -106,8 +106,12 @@ int32_t actor_check_dims(int d, int H, int A, ErrBuf &err);
 // W1 [H][d] -> [H][roundup(d,4)] zero padded (16-byte aligned rows for cp.async)
 int32_t actor_pad_w1_launch(const float *params, int H, int d, float *w1p, cudaStream_t stream, ErrBuf &err);
 int32_t actor_forward_launch(const float *pi_params, const float *pi_w1p, const float *vf_params,
-                             const float *vf_w1p, int d, int H, int A, const float *obs, const float *mask,
-                             int64_t batch, uint64_t seed, uint64_t offset, const int64_t *force_act, int64_t *act,
-                             float *logp_a, float *v, float *probs, float *logits, cudaStream_t stream, ErrBuf &err);
+                             const float *vf_w1p, const unsigned char *pi_pack, const unsigned char *vf_pack, int d, int H, int A,
+                             const float *obs, const float *mask, int64_t batch, uint64_t seed, uint64_t offset,
+                             const int64_t *force_act, int64_t *act, float *logp_a, float *v, float *probs, float *logits,
+                             cudaStream_t stream, ErrBuf &err);
+// bf16x3 weight planes for the tensor-core actor kernel (actor_tc.cu); 0 bytes when the shape is not supported there
+size_t actor_pack_bytes(int d, int H);
+int32_t actor_pack_launch(const float *params, int d, int H, int out, unsigned char *pack, cudaStream_t stream, ErrBuf &err);
 
 }  // namespace rrl

@@ -69,6 +69,7 @@ struct rrl_actor {
     rrl::ErrBuf err;
     cudaStream_t stream = nullptr;
     float *pi_params = nullptr, *pi_w1p = nullptr, *vf_params = nullptr, *vf_w1p = nullptr;
+    unsigned char *pi_pack = nullptr, *vf_pack = nullptr;  // bf16x3 planes for the tensor-core kernel (null: shape not supported)
     // device mirrors of the host-facing buffers of rrl_actor_step
     float *d_obs = nullptr, *d_mask = nullptr, *d_logp = nullptr, *d_v = nullptr, *d_probs = nullptr, *d_logits = nullptr;
     int64_t *d_act = nullptr;

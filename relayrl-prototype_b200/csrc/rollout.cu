@@ -136,7 +136,7 @@ extern "C" int32_t rrl_rollout_step(rrl_rollout_t *r, const float *obs, const fl
     RRL_CUDA_OK(cudaMemcpyAsync(a->d_mask, mask, B * a->A * 4, cudaMemcpyHostToDevice, st), r->err);
     RRL_CUDA_OK(cudaMemcpyAsync(r->d_rew_in, reward, B * 4, cudaMemcpyHostToDevice, st), r->err);
     RRL_CUDA_OK(cudaMemcpyAsync(r->d_len, r->len.data(), B * 4, cudaMemcpyHostToDevice, st), r->err);
-    int32_t s = actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->d, a->H,
+    int32_t s = actor_forward_launch(a->pi_params, a->pi_w1p, a->with_baseline ? a->vf_params : nullptr, a->vf_w1p, a->pi_pack, a->vf_pack, a->d, a->H,
                                      a->A, a->d_obs, a->d_mask, N, seed, offset, nullptr, a->d_act, a->d_logp, a->d_v, nullptr,
                                      nullptr, st, r->err);
     if (s != RRL_OK) return s;

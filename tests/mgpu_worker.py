@@ -37,7 +37,13 @@ def main():
     obs = rng.standard_normal((n, d)).astype(np.float32)
     act = rng.integers(0, A, n).astype(np.float32)
     mask = np.ones((n, A), np.float32)
-    rew = rng.uniform(-1, 1, n).astype(np.float32)
+    # rewards the value net can learn (a smooth function of the observation plus a little noise): over the 80 Adam steps
+    # the gradient then stays well above float32 summation noise.  With pure-noise rewards the net fits the mean within a
+    # few steps, every gradient entry becomes noise, Adam normalises that noise to steps of +-lr, and two correct float32
+    # runs random-walk up to 80 lr apart (measured: 0.059 between the 1-GPU and the 2-GPU run, with all losses within
+    # 1e-5) -- that would test Adam's conditioning, not the data-parallel path.
+    w_true = rng.standard_normal(d).astype(np.float32)
+    rew = (0.5 * np.tanh(obs @ w_true) + 0.05 * rng.uniform(-1, 1, n)).astype(np.float32)
     val = rng.standard_normal(n).astype(np.float32)
     logp = rng.standard_normal(n).astype(np.float32)
     lvs = rng.uniform(-1, 1, E).astype(np.float32)
@@ -89,11 +95,20 @@ def main():
             e = np.abs(np.asarray(a, np.float64) - np.asarray(b, np.float64))
             return float((e <= 5e-7 + 1e-5 * np.abs(b)).mean()), float(e.max())
 
-        for name, got, want, lr in (("policy", pi_dp, S.get_params(0), 3e-4), ("value", v_dp, S.get_params(1), 1e-3)):
+        for which, name, got, want, lr in ((0, "policy", pi_dp, S.get_params(0), 3e-4), (1, "value", v_dp, S.get_params(1), 1e-3)):
             frac, emax = strict(got, want)
-            print("MGPU %s vs 1 GPU: strict %.5f max abs err %.3g" % (name, frac, emax), flush=True)
+            # what Adam's conditioning explains (tests/test_gpu_learner.py::assert_weights_close): float32 summation noise of
+            # 3e-7 of the largest gradient entry per step, divided by this weight's own sqrt(v_hat) + eps, 80 steps
+            m_, v_, step_ = S.get_opt_state(which)
+            sv = np.sqrt(v_ / (1.0 - 0.999 ** step_))
+            cond = min(step_, 80) * 3e-7 * sv.max() / (sv + 1e-8)
+            err = np.abs(got.astype(np.float64) - want)
+            unexplained = err > 5e-7 + 1e-5 * np.abs(want) + lr * cond
+            print("MGPU %s vs 1 GPU: strict %.5f max abs err %.3g (%.3g lr); beyond conditioning: %d of %d; sqrt(v_hat) min %.3g "
+                  "median %.3g max %.3g" % (name, frac, emax, emax / lr, int(unexplained.sum()), len(got), sv.min(),
+                                            np.median(sv), sv.max()), flush=True)
             assert frac >= 0.999, "%s: strict agreement with the 1-GPU run %.5f" % (name, frac)
-            np.testing.assert_allclose(got, want, rtol=1e-5, atol=0.1 * lr)
+            assert not unexplained.any(), "%s: %d weights differ by more than their conditioning explains" % (name, int(unexplained.sum()))
         if with_oracle:
             # ... and against the oracle (the reference's arithmetic on the host): float32, and float64 as the
             # tie-breaker -- the data-parallel result must be as close to the float64 truth as the reference is
