@@ -302,6 +302,15 @@ def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=655
             ev[i - 3][1].record(st)
     torch.cuda.synchronize()
     ms = sorted(a.elapsed_time(b) for a, b in ev)[reps // 2]
+    # end to end: the host-buffer call an agent makes (rrl_actor_step): obs and mask from pinned host memory, act / logp_a /
+    # v back on the host, wall clock around the (synchronous) call
+    obs_np, mask_np = obs_h.pin_memory().numpy(), mask_h.pin_memory().numpy()
+    e2e = []
+    for i in range(3 + reps):
+        t0 = time.perf_counter()
+        act.step(obs_np, mask_np, seed=4, offset=100 + i)
+        e2e.append(time.perf_counter() - t0)
+    e2e_ms = sorted(e2e[3:])[reps // 2] * 1e3
     act.close()
     # CPU baseline leg: the oracle's restatement of PolicyWithBaseline.step on the same weights
     from oracle import learner_oracle as lo
@@ -315,6 +324,10 @@ def measure_actor(dev, batch=65536, d=128, A_=18, H_=256, reps=20, cpu_batch=655
     flops = 2.0 * (d * H_ + H_ * H_ + H_ * A_) + 2.0 * (d * H_ + H_ * H_ + H_)
     return {"workload": "C4: batch %d, d=%d, A=%d, H=%d, with baseline (policy + value + sampling per env)" % (batch, d, A_, H_),
             "env_steps_per_s": batch / (ms * 1e-3), "ms_per_call": ms, "tflops": flops * batch / (ms * 1e-3) / 1e12,
+            "executed_bf16_tflops": 6.0 * 4.0 * (d * H_ + H_ * H_) * batch / (ms * 1e-3) / 1e12,
+            "kernel": "actor_tc_kernel<256> (tcgen05, bf16x3)",
+            "e2e": {"env_steps_per_s": batch / (e2e_ms * 1e-3), "ms_per_call": e2e_ms,
+                    "h2d_bytes_per_call": batch * (d + A_) * 4, "d2h_bytes_per_call": batch * 16},
             "cpu_env_steps_per_s": cpu_batch / cpu_s, "cpu_cores": os.cpu_count() or 1, "cpu_kind": "port"}
 
 

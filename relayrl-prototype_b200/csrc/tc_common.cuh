@@ -201,6 +201,20 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}\n" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// one arrival that also announces `bytes` of asynchronous (bulk-copy) traffic still to land on this barrier
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// TMA bulk copy (no tensor map): `bytes` contiguous bytes global -> this CTA's shared memory, completion counted on `bar`.
+// Source, destination and size are multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 // ---- TMEM -> registers: 32 lanes x 32 consecutive 32-bit columns (thread = lane) -------------------------
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
 {

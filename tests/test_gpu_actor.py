@@ -82,3 +82,37 @@ def test_actor_c4_shape_runs():
     np.testing.assert_allclose(data["v"][idx], ref["v"].numpy(), rtol=1e-5, atol=1e-6)
     assert (mask[np.arange(B), act] == 1).all()
     a.close()
+
+
+@pytest.mark.parametrize("d,A,H,wb,B", [(20, 5, 256, True, 1000), (128, 32, 256, False, 129), (8, 1, 128, True, 128),
+                                        (3, 2, 128, True, 5000)])
+def test_actor_tensor_core_path_ragged_shapes(d, A, H, wb, B):
+    """The tcgen05 kernel (csrc/actor_tc.cu: batch >= 128, hidden 128 or 256, obs_dim <= 128) against the oracle on shapes
+    that exercise its edges: a partial last tile, obs_dim that is not a multiple of 8 or 16 (zero-padded K), the widest
+    head, a single action, no value net, more tiles than SMs would take in one wave is covered by the C4 test."""
+    from relayrl_b200 import Actor
+    pi, v = lo.init_params(d, H, A, 11), lo.init_params(d, H, 1, 12)
+    a = Actor(d, A, hidden=H, with_baseline=wb, max_batch=B)
+    a.set_params(0, lo.flatten(pi).numpy())
+    if wb:
+        a.set_params(1, lo.flatten(v).numpy())
+    rng = np.random.default_rng(d * 1000 + A)
+    obs = (rng.standard_normal((B, d)) * 2).astype(np.float32)
+    mask = (rng.random((B, A)) > 0.3).astype(np.float32)
+    mask[:, 0] = 1
+    act, data, probs, logits = a.step(obs, mask, seed=9, offset=3, want_probs=True)
+    _, ref = lo.actor_step(pi, v if wb else None, torch.from_numpy(obs), torch.from_numpy(mask), act=torch.from_numpy(act))
+    np.testing.assert_allclose(logits, ref["logits"].numpy(), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(probs, ref["probs"].numpy(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(data["logp_a"], ref["logp_a"].numpy(), rtol=1e-5, atol=1e-6)
+    if wb:
+        np.testing.assert_allclose(data["v"], ref["v"].numpy(), rtol=1e-5, atol=1e-6)
+    assert (mask[np.arange(B), act] == 1).all()
+    # the same draw as the CUDA-core kernel makes from the same probabilities: both use Philox(seed, offset + row)
+    small = Actor(d, A, hidden=H, with_baseline=wb, max_batch=B)
+    small.set_params(0, lo.flatten(pi).numpy())
+    if wb:
+        small.set_params(1, lo.flatten(v).numpy())
+    acts = np.concatenate([small.step(obs[i:i + 100], mask[i:i + 100], seed=9, offset=3 + i)[0] for i in range(0, B, 100)])
+    assert (acts == act).mean() > 0.999      # (a draw within float32 rounding of a CDF step may fall either way)
+    a.close(), small.close()

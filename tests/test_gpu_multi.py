@@ -13,12 +13,14 @@ from conftest import ROOT
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("iters", [3, 80])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_data_parallel_matches_single_gpu(world):
+def test_data_parallel_matches_single_gpu(world, iters):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
-    port = 29600 + world
+    port = 29600 + world + (100 if iters == 80 else 0)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, MGPU_ITERS=str(iters)))
+    print(r.stdout[-3000:])
     assert r.returncode == 0 and "MGPU_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-4000:])
