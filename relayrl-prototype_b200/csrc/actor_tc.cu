@@ -22,6 +22,8 @@
 // five small products of every K step are accumulated first (cross pass) and the K/16 main products last (main pass,
 // which re-streams plane 1 of the weights: 4/3 of the bytes, 16 instead of 96 MMAs at full accumulator size).
 #include "actor_internal.cuh"
+#include <type_traits>
+
 #include "tc_common.cuh"
 
 namespace rrl {
@@ -104,6 +106,18 @@ constexpr int AT_SMEM_BYTES = OFF_BAR + (2 * AT_STAGES + 3) * 8 + 8;
 static_assert(AT_SMEM_BYTES <= 227 * 1024, "tensor-core actor kernel exceeds shared memory");
 static_assert(OFF_RING % 128 == 0 && OFF_BAR % 8 == 0, "alignment");
 
+// developer timing variants (make actor_variants; wrong results, never shipped)
+#ifdef AT_DBG_NO_FULL_WAIT
+#define AT_WAIT_FULL(bar, ph) ((void)0)
+#else
+#define AT_WAIT_FULL(bar, ph) mbar_wait(bar, ph)
+#endif
+#ifdef AT_DBG_NO_MMA
+#define AT_MMA(x) ((void)0)
+#else
+#define AT_MMA(x) x
+#endif
+
 template <int H>
 __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
 {
@@ -149,16 +163,16 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
     if (warp == AT_WORKERS / 32 + 1) {
         // ---- producer: the packed weights of each net, block after block, into the ring -------------------------------
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t st = 0, ph = 0;
             const int per_net = ps.per_net();
             for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x)
                 for (int net = 0; net < nets; ++net) {
                     const unsigned char *src = net ? a.vf.pack : a.pi.pack;
-                    for (int b = 0; b < per_net; ++b, ++it) {
-                        const uint32_t st = it % AT_STAGES, ph = (it / AT_STAGES) & 1u;
+                    for (int b = 0; b < per_net; ++b) {
                         mbar_wait(&empty[st], ph ^ 1u);  // (passes at once the first time round)
                         mbar_arrive_expect_tx(&full[st], AT_BLOCK);
                         bulk_g2s(ring + st * AT_BLOCK, src + (size_t)b * AT_BLOCK, AT_BLOCK, &full[st]);
+                        if (++st == AT_STAGES) st = 0, ph ^= 1u;
                     }
                 }
         }
@@ -166,43 +180,66 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         // ---- the MMA warp (converged; one elected lane issues) --------------------------------------------------------
         constexpr uint32_t IDESC = idesc_bf16(AT_M, AT_NCHUNK, false, false);
         const uint32_t ring_u = smem_u32(ring), obs_u = smem_u32(obs_p);
-        uint32_t it = 0, chunk_n = 0, tcount = 0;
+        // Descriptors are built once per ring block (one move into uniform registers) and stepped by compile-time constants:
+        // with a descriptor computed per MMA the issue loop ran at 161 cycles per MMA instead of the tensor core's 64.
+        constexpr uint64_t SUBQ = AT_SUB >> 4, PLQ = OBS_PLANE >> 4;
+        uint32_t st = 0, ph = 0, chunk_n = 0, tcount = 0;
+        auto next_stage = [&]() {
+            if (++st == AT_STAGES) st = 0, ph ^= 1u;
+        };
+        auto run_chunk = [&](auto l1_tag, int ks) {
+            constexpr bool L1 = decltype(l1_tag)::value;
+            const uint32_t acc_t = tmem + AT_TM_ACC;
+            for (int s = 0; s < ks; ++s) {  // cross pass: the five small products of K step s
+                AT_WAIT_FULL(&full[st], ph);
+                const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 2048, 128);
+                if (L1) {
+                    const uint64_t ad = smem_desc(obs_u + s * 2 * OBS_CHUNK, OBS_CHUNK, 128);
+                    AT_MMA(mma_bf16_elect(acc_t, ad, bd + 2 * SUBQ, IDESC, s > 0));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + 2 * PLQ, bd, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd, IDESC, true));
+                } else {
+                    const uint32_t at = tmem + AT_TM_A + 8 * s;
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + 2 * SUBQ, IDESC, s > 0));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 256, bd, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd, IDESC, true));
+                }
+                mma_commit_warp(&empty[st]);
+                next_stage();
+            }
+            for (int s0 = 0; s0 < ks; s0 += 3) {  // main pass: plane 1 x plane 1, three K steps per block
+                AT_WAIT_FULL(&full[st], ph);
+                const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 2048, 128);
+#pragma unroll
+                for (int j = 0; j < 3; ++j)
+                    if (s0 + j < ks) {
+                        if (L1)
+                            AT_MMA(mma_bf16_elect(acc_t, smem_desc(obs_u + (s0 + j) * 2 * OBS_CHUNK, OBS_CHUNK, 128), bd + j * SUBQ, IDESC, true));
+                        else
+                            AT_MMA(mma_bf16_ts_elect(acc_t, tmem + AT_TM_A + 8 * (s0 + j), bd + j * SUBQ, IDESC, true));
+                    }
+                mma_commit_warp(&empty[st]);
+                next_stage();
+            }
+        };
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
             mbar_wait(a_ready, tcount & 1u);  // this tile's observation planes are in shared memory
             fence_after_sync();
             for (int net = 0; net < nets; ++net)
-                for (int layer = 1; layer <= 2; ++layer) {
-                    const int ks = layer == 1 ? ps.ks1 : ps.ks2;
+                for (int layer = 1; layer <= 2; ++layer)
                     for (int c = 0; c < NC; ++c, ++chunk_n) {
                         mbar_wait(acc_empty, (chunk_n & 1u) ^ 1u);  // the epilogue has read the previous chunk
                         fence_after_sync();
-                        bool acc = false;
-                        auto mma = [&](int pa, int s, uint32_t b_addr) {
-                            const uint64_t bd = smem_desc(b_addr, 2048, 128);
-                            if (layer == 1)
-                                mma_bf16_elect(tmem + AT_TM_ACC, smem_desc(obs_u + pa * OBS_PLANE + s * 2 * OBS_CHUNK, OBS_CHUNK, 128), bd, IDESC, acc);
-                            else
-                                mma_bf16_ts_elect(tmem + AT_TM_ACC, tmem + AT_TM_A + pa * 128 + 8 * s, bd, IDESC, acc);
-                            acc = true;
-                        };
-                        for (int s = 0; s < ks; ++s, ++it) {  // cross pass: the five small products of K step s
-                            const uint32_t st = it % AT_STAGES, ph = (it / AT_STAGES) & 1u;
-                            mbar_wait(&full[st], ph);
-                            const uint32_t b0 = ring_u + st * AT_BLOCK;
-                            mma(0, s, b0 + 2 * AT_SUB), mma(1, s, b0 + AT_SUB), mma(2, s, b0);
-                            mma(0, s, b0 + AT_SUB), mma(1, s, b0);
-                            mma_commit_warp(&empty[st]);
-                        }
-                        for (int s0 = 0; s0 < ks; s0 += 3, ++it) {  // main pass: plane 1 x plane 1, three K steps per block
-                            const uint32_t st = it % AT_STAGES, ph = (it / AT_STAGES) & 1u;
-                            mbar_wait(&full[st], ph);
-                            const uint32_t b0 = ring_u + st * AT_BLOCK;
-                            for (int j = 0; j < 3 && s0 + j < ks; ++j) mma(0, s0 + j, b0 + j * AT_SUB);
-                            mma_commit_warp(&empty[st]);
-                        }
+                        if (layer == 1)
+                            run_chunk(std::true_type{}, ps.ks1);
+                        else
+                            run_chunk(std::false_type{}, H / 16);
                         mma_commit_warp(acc_full);
                     }
-                }
         }
     } else {
         // ---- the eight worker warps: thread = environment (TMEM lane), column half hf ------------------------------------
@@ -282,6 +319,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     load_chunk(v, b1, c);
                     const bool last = c + 1 == NC;
                     if (!last) arrive(acc_empty);  // the next chunk of layer 1 may overwrite the accumulator already
+#ifndef AT_DBG_NO_EPI
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
                         uint32_t p1[8], p2[8], p3[8];
@@ -293,6 +331,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                         const uint32_t col = tmem_lane + AT_TM_A + 64 * c + 32 * hf + 8 * g;  // unit / 2
                         tmem_st8(col, p1), tmem_st8(col + 128, p2), tmem_st8(col + 256, p3);
                     }
+#else
+                    if (v[3] == 123.f) vcomb_s[row] = v[5];
+#endif
                     if (last) {
                         arrive(acc_empty);  // layer 2 reads the planes: only now
                         // every MMA that reads the observation planes has retired: the next tile's can be built under layer 2
@@ -312,6 +353,10 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     load_chunk(v, b2, c);
                     arrive(acc_empty);  // the values are in registers: the tensor core moves on while the head is summed
                     const float *wc = w3 + AT_NCHUNK * c + 64 * hf;
+#ifdef AT_DBG_NO_EPI
+                    head[0] += v[7];
+                    if (false)
+#endif
 #pragma unroll
                     for (int a0 = 0; a0 < AT_MAX_A; a0 += 4)
                         if (a0 < outs4) {

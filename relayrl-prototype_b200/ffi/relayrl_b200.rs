@@ -43,6 +43,22 @@ extern "C" {
                                   logp: *const u8, logp_len: usize, done: u8) -> i32;
     pub fn rrl_train_epoch(h: *mut c_void, stats: *mut RrlEpochStats) -> i32;
     pub fn rrl_last_error(h: *const c_void) -> *const c_char;
+    // the ZMQ transport's message body: serde_pickle of Vec<RelayRLAction> (training_zmq.rs:994-1001), as received
+    pub fn rrl_ingest_pickle(h: *mut c_void, msg: *const u8, len: usize, n_actions: *mut i64) -> i32;
+    // weights, Adam state and the buffer's stale adv/ret tail (the reference keeps none of it across a restart)
+    pub fn rrl_checkpoint_save(h: *mut c_void, path: *const c_char, user_tag: u64) -> i32;
+    pub fn rrl_checkpoint_load(h: *mut c_void, path: *const c_char, user_tag: *mut u64) -> i32;
+    // batched agent: request_for_action / flag_last_action for n_envs environments per call (agent_zmq.rs:458-610)
+    pub fn rrl_actor_create(obs_dim: i32, act_dim: i32, hidden: i32, with_baseline: i32, device: i32, max_batch: i64,
+                            out: *mut *mut c_void) -> i32;
+    pub fn rrl_actor_set_params(a: *mut c_void, which: i32, flat: *const f32, n: i64) -> i32;
+    pub fn rrl_actor_step(a: *mut c_void, obs: *const f32, mask: *const f32, batch: i64, seed: u64, offset: u64,
+                          act: *mut i64, logp_a: *mut f32, v: *mut f32, probs: *mut f32, logits: *mut f32) -> i32;
+    pub fn rrl_rollout_create(actor: *mut c_void, learner: *mut c_void, n_envs: i64, max_len: i64, out: *mut *mut c_void) -> i32;
+    pub fn rrl_rollout_step(r: *mut c_void, obs: *const f32, mask: *const f32, reward: *const f32, seed: u64, offset: u64,
+                            act: *mut i64, logp_a: *mut f32, v: *mut f32) -> i32;
+    pub fn rrl_rollout_flag_last(r: *mut c_void, env_ids: *const i64, rewards: *const f32, count: i64) -> i32;
+    pub fn rrl_rollout_destroy(r: *mut c_void) -> i32;
 }
 
 /// Safe wrapper: one learner = one GPU; `&mut self` serialises calls like the worker's asyncio.Lock.
@@ -62,6 +78,12 @@ impl B200Learner {
         let st = unsafe { rrl_ingest_wire_action(self.0, obs.as_ptr(), obs.len(), act.as_ptr(), act.len(),
             mask.as_ptr(), mask.len(), rew, v.as_ptr(), v.len(), logp.as_ptr(), logp.len(), done as u8) };
         if st != 0 { Err(last_error(self.0)) } else { Ok(()) }
+    }
+    /// The ZMQ server's loop body: one pickled trajectory as it came off the socket.
+    pub fn ingest_pickle(&mut self, msg: &[u8]) -> Result<i64, String> {
+        let mut n = 0i64;
+        let st = unsafe { rrl_ingest_pickle(self.0, msg.as_ptr(), msg.len(), &mut n) };
+        if st != 0 { Err(last_error(self.0)) } else { Ok(n) }
     }
     pub fn train_epoch(&mut self) -> Result<RrlEpochStats, String> {
         let mut s = RrlEpochStats::default();

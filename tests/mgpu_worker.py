@@ -162,7 +162,8 @@ def main():
                       % (name, f_gpu, f_ref, f_one, m_gpu, m_ref, m_one), flush=True)
                 assert f_gpu >= min(f_ref, f_one, 0.999) - 0.02, (name, f_gpu, f_ref, f_one)
                 assert m_gpu <= 2.0 * max(m_ref, m_one) + 0.01 * lr, (name, m_gpu, m_ref, m_one)
-                if few or which == 0:
+                if f_ref >= 0.999:   # (where the float32 reference itself is well-conditioned; after 3 value steps it keeps
+                    # 97.5 % within the strict bound of its float64 run, max 0.56 lr: gradient entries below Adam's eps)
                     np.testing.assert_allclose(got, w32, rtol=1e-5, atol=0.1 * lr)
         S.close()
         print("MGPU_OK world=%d n=%d" % (world, n))
