@@ -239,10 +239,10 @@ def measure_scan(cols, offsets, last_vals, n, dev, with_baseline=True, reps=20):
     return sorted(a.elapsed_time(b) for a, b in zip(e0, e1))[reps // 2]
 
 
-# (21.161472 MB + 0.147968 MB) / 1 048 576 transitions, profiles/r1_tc_kernel_ncu_full_metrics.csv
-NCU_VALUE_KERNEL_BYTES_PER_TRANSITION = (21161472 + 147968) / 1048576.0
-# (537.989120 MB + 485.492736 MB) / 67 108 864 transitions, profiles/r1_scan_kernel_ncu_full_metrics.csv
-NCU_SCAN_KERNEL_BYTES_PER_TRANSITION = (537989120 + 485492736) / 67108864.0
+# (21.150976 MB + 0.020480 MB) / 1 048 576 transitions, profiles/r2_tc_kernel_metrics.csv
+NCU_VALUE_KERNEL_BYTES_PER_TRANSITION = (21150976 + 20480) / 1048576.0
+# (551.635456 MB + 487.865856 MB) / 67 108 864 transitions, profiles/r2_scan_kernel_metrics.csv
+NCU_SCAN_KERNEL_BYTES_PER_TRANSITION = (551635456 + 487865856) / 67108864.0
 
 
 def linear_init(d, hidden, out, seed):
@@ -613,16 +613,16 @@ def run_ours(args):
                      "bound": "tensor", "achieved": achieved_tf, "peak": bf16_sust, "unit": "TFLOP/s",
                      "frac": achieved_tf / bf16_sust, "traffic": NCU_VALUE_KERNEL_BYTES_PER_TRANSITION * n,
                      "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture at 1 Mi "
-                                       "transitions (profiles/r1_tc_kernel_ncu_full_metrics.csv), scaled per transition; "
+                                       "transitions (profiles/r2_tc_kernel_metrics.csv), scaled per transition; "
                                        "algorithmic bytes are 20 per transition",
                      "peak_source": which + " bf16 sustained",
                      "flops_per_launch": flops_per_launch, "launch_ms": value_launch_ms,
                      "executed_bf16_tflops": 6.0 * 3 * 2 * H * H * n / (value_launch_ms * 1e-3) / 1e12,
                      "note": "achieved = algorithmic fp32 flops (6*(D*H+H*H+H) per transition); each fp32 GEMM "
                              "is six bf16 MMAs (bf16x3 split), executed_bf16_tflops counts those"},
-        "roofline_scan": {"kernel": "scan_kernel<with_baseline>", "bound": "hbm", "achieved": scan_gbs, "peak": hbm,
+        "roofline_scan": {"kernel": "scan_chunk_kernel<with_baseline>", "bound": "hbm", "achieved": scan_gbs, "peak": hbm,
                           "unit": "GB/s", "frac": scan_gbs / hbm, "traffic": NCU_SCAN_KERNEL_BYTES_PER_TRANSITION * n,
-                          "traffic_source": "ncu --set full at 64 Mi transitions (profiles/r1_scan_kernel_ncu_full_metrics.csv), "
+                          "traffic_source": "ncu --set full at 64 Mi transitions (profiles/r2_scan_kernel_metrics.csv), "
                                             "scaled per transition", "peak_source": which,
                           "bytes_per_transition": 16, "launch_ms": scan_ms},
         "stage_ms": {"scan": s["ms_scan"], "policy": s["ms_policy"], "value": s["ms_value"]},

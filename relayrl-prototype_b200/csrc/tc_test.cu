@@ -136,6 +136,7 @@ extern "C" int32_t rrl_debug_tc_gemm(int32_t mode, const float *A, const float *
 namespace rrl {
 namespace {
 using namespace tc;
+template <bool TS>
 __global__ void __launch_bounds__(128, 1) tc_rate_kernel(int N, int a_mn, int b_mn, int count, int uniform_issue, long long *out)
 {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -168,7 +169,10 @@ __global__ void __launch_bounds__(128, 1) tc_rate_kernel(int N, int a_mn, int b_
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 const int ss = s % ksteps;
-                mma_bf16_elect(tmem, da + ((ss * a_k) >> 4), db + ((ss * b_k) >> 4), idesc, (i + s) > 0);
+                if (TS)  // A from tensor memory (columns 128..191), N <= 128
+                    mma_bf16_ts_elect(tmem, tmem + 128 + 8 * ss, db + ((ss * b_k) >> 4), idesc_bf16(128, N, false, b_mn != 0), (i + s) > 0);
+                else
+                    mma_bf16_elect(tmem, da + ((ss * a_k) >> 4), db + ((ss * b_k) >> 4), idesc, (i + s) > 0);
             }
         }
         if (elect_one()) mma_commit(&bar);
@@ -208,9 +212,14 @@ __global__ void __launch_bounds__(128, 1) tc_rate_kernel(int N, int a_mn, int b_
 extern "C" int32_t rrl_debug_tc_rate(int32_t N, int32_t a_mn, int32_t b_mn, int32_t count, int32_t uniform_issue, long long *out_dev, void *stream)
 {
     using namespace rrl;
-    if (N < 16 || N > 256 || N % 16 || count < 4 || count % 4 || !out_dev) return RRL_EINVAL;
+    if (N < 16 || N > 256 || N % 16 || count < 4 || count % 4 || !out_dev || (a_mn == 2 && (N > 128 || !uniform_issue))) return RRL_EINVAL;
     const size_t smem = (size_t)rrl::tc::x_plane_bytes(128, 128) + rrl::tc::x_plane_bytes(N, 128);
-    if (cudaFuncSetAttribute(tc_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
-    tc_rate_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(N, a_mn, b_mn, count, uniform_issue, out_dev);
+    if (a_mn == 2) {
+        if (cudaFuncSetAttribute(tc_rate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
+        tc_rate_kernel<true><<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(N, 0, b_mn, count, uniform_issue, out_dev);
+    } else {
+        if (cudaFuncSetAttribute(tc_rate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return RRL_ECUDA;
+        tc_rate_kernel<false><<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(N, a_mn, b_mn, count, uniform_issue, out_dev);
+    }
     return cudaGetLastError() == cudaSuccess ? RRL_OK : RRL_ECUDA;
 }
