@@ -288,13 +288,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         };
         // this thread's 64 accumulator columns of the current chunk, bias added, relu applied
         auto load_chunk = [&](float (&v)[64], const float *bias, int c) {
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                float t[16];
-                tmem_ld16(tmem_lane + AT_TM_ACC + 64 * hf + 16 * g, t);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[16 * g + i] = t[i];
-            }
+            tmem_ld64(tmem_lane + AT_TM_ACC + 64 * hf, v);
             const float *bb = bias + AT_NCHUNK * c + 64 * hf;
 #pragma unroll
             for (int i = 0; i < 64; i += 4) {
@@ -329,8 +323,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                             p1[i >> 1] = pack_hi16(s0.t1, s1.t1), p2[i >> 1] = pack_hi16(s0.t2, s1.t2), p3[i >> 1] = pack_hi16(s0.t3, s1.t3);
                         }
                         const uint32_t col = tmem_lane + AT_TM_A + 64 * c + 32 * hf + 8 * g;  // unit / 2
-                        tmem_st8(col, p1), tmem_st8(col + 128, p2), tmem_st8(col + 256, p3);
+                        tmem_st8_nowait(col, p1), tmem_st8_nowait(col + 128, p2), tmem_st8_nowait(col + 256, p3);
                     }
+                    tmem_st_wait();
 #else
                     if (v[3] == 123.f) vcomb_s[row] = v[5];
 #endif

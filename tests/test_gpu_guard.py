@@ -53,7 +53,7 @@ def test_scan_stays_inside_its_buffers(n, with_baseline):
             (adv_f, adv), (ret_f, ret) = guarded(n), guarded(n)
             ws_f, ws = guarded(wsb // 8, torch.float64)
             st_f, st = guarded(6, torch.float64)
-            adv.zero_(), ret.zero_()
+            adv.zero_(), ret.zero_(), st.zero_()     # (slot 5 of the statistics is written by the multi-rank merge only)
         scan_device(rew, val, d_offs, lvs, n, n_ep, 0.98, 0.95, with_baseline, adv, ret, st, ws)
         torch.cuda.synchronize()
         out[name] = (adv.clone(), ret.clone(), st.clone())
