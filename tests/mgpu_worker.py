@@ -72,8 +72,12 @@ def main():
 
     eb = shard_episodes(offs, world)
     lo_, hi, loc = shard_rows(offs, eb, rank)
+    # the same kernel on every shard size: at 4 and 8 GPUs a shard (< 32 768 rows) would otherwise take the CUDA-core kernel
+    # while the 1-GPU run takes the tensor-core one (measured: the two paths' policy gradients differ by 8e-6 in rel L2 at
+    # this size -- ReLU decisions -- which is a statement about the kernels, not about the data-parallel exchange)
+    flags = int(os.environ.get("MGPU_FLAGS", "1"))     # RRL_FLAG_TC_ANY_SIZE
     L = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, device=local, rank=rank,
-                nranks=world, nccl_id=nccl_id)
+                nranks=world, nccl_id=nccl_id, flags=flags)
     L.set_params(0, pi0), L.set_params(1, v0)
     g_dp = []
     res = run(L, lo_, hi, loc, lvs[eb[rank]:eb[rank + 1]], grads=g_dp)
@@ -88,7 +92,7 @@ def main():
     L.close()
     if rank == 0:
         assert np.array_equal(merge_offsets(gathered), offs)       # offsets identical after concatenation
-        S = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, device=local)
+        S = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, device=local, flags=flags)
         S.set_params(0, pi0), S.set_params(1, v0)
         g_one = []
         ref = run(S, 0, n, offs, lvs, grads=g_one)
