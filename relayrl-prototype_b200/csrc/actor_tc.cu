@@ -33,8 +33,7 @@ namespace {
 using namespace tc;
 
 constexpr int AT_M = 128;           // environments per tile
-constexpr int AT_NCHUNK = 128;      // hidden units per accumulator chunk of layer 1
-constexpr int AT_NSUB = 64;         // ... and per sub-chunk of layer 2 (two 64-column accumulators in turn)
+constexpr int AT_NCHUNK = 128;      // hidden units per accumulator chunk
 constexpr int AT_MAX_DK = 128;      // obs_dim rounded up to 16
 constexpr int AT_MAX_A = 32;
 constexpr int AT_SUB = 4096;        // bytes of one (k-step, plane) piece of a weight chunk: 128 units x 16 k, bf16
@@ -45,24 +44,20 @@ constexpr int AT_THREADS = AT_WORKERS + 64;  // + the MMA warp + the producer wa
 constexpr uint32_t AT_TM_ACC = 0, AT_TM_A = 128, AT_TM_COLS = 512;  // accumulator | three planes of 128 columns
 
 struct PackShape {
-    // K steps of the two layers; layer 1 runs in chunks of 128 units, layer 2 in sub-chunks of 64; ring blocks per chunk
-    int dK, ks1, ks2, nc, nc2, blocks1, blocks2;
-    __host__ __device__ int per_net() const { return nc * blocks1 + nc2 * blocks2; }
+    int dK, ks1, ks2, nc, blocks1, blocks2;  // K steps of the two layers, unit chunks, ring blocks per (layer, chunk)
+    __host__ __device__ int per_net() const { return nc * (blocks1 + blocks2); }
 };
 __host__ __device__ inline PackShape pack_shape(int d, int H)
 {
     PackShape s;
-    s.dK = (d + 15) & ~15, s.ks1 = s.dK / 16, s.ks2 = H / 16, s.nc = H / AT_NCHUNK, s.nc2 = H / AT_NSUB;
-    s.blocks1 = s.ks1 + (s.ks1 + 2) / 3, s.blocks2 = s.ks2 / 2 + (s.ks2 + 5) / 6;
+    s.dK = (d + 15) & ~15, s.ks1 = s.dK / 16, s.ks2 = H / 16, s.nc = H / AT_NCHUNK;
+    s.blocks1 = s.ks1 + (s.ks1 + 2) / 3, s.blocks2 = s.ks2 + (s.ks2 + 2) / 3;
     return s;
 }
 
-// Packed stream of one net, in 12 KB ring blocks.
-//   layer 1, for each chunk of 128 units: [cross blocks: K step s -> planes 1, 2, 3 of that step] [main blocks: group g ->
-//     plane 1 of K steps 3g, 3g+1, 3g+2]; a 4 KB piece holds unit n, k at byte (k / 8) * 2048 + n * 16 + (k % 8) * 2
-//   layer 2, for each sub-chunk of 64 units: [cross blocks: K steps 2b, 2b+1 -> planes 1, 2, 3 each] [main blocks: plane 1
-//     of K steps 6g .. 6g+5]; a 2 KB piece holds unit n, k at byte (k / 8) * 1024 + n * 16 + (k % 8) * 2
-// i.e. the un-swizzled K-major core-matrix layout (SBO 128, LBO = bytes of one 8-k column of the piece).
+// Packed stream of one net: for layer in (1, 2): for chunk c: [cross blocks: K step s -> planes 1, 2, 3 of that step]
+// [main blocks: group g -> plane 1 of K steps 3g, 3g+1, 3g+2].  A piece holds unit n (of the chunk), k (of the step) at
+// byte (k / 8) * 2048 + n * 16 + (k % 8) * 2: the un-swizzled K-major core-matrix layout (LBO 2048, SBO 128).
 __global__ void __launch_bounds__(256) actor_pack_kernel(const float *__restrict__ params, int d, int H, int out,
                                                          unsigned short *__restrict__ pack)
 {
@@ -72,31 +67,23 @@ __global__ void __launch_bounds__(256) actor_pack_kernel(const float *__restrict
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         int blk = (int)(i / (AT_BLOCK / 2));
         const int e = (int)(i - (int64_t)blk * (AT_BLOCK / 2));
+        const int sub = e / (AT_SUB / 2), w = e - sub * (AT_SUB / 2);  // element within the piece
+        const int kc = w / 1024, n = (w - kc * 1024) / 8, k8 = w & 7;
+        int layer = 1, per = ps.blocks1, ks = ps.ks1;
+        if (blk >= ps.nc * ps.blocks1) blk -= ps.nc * ps.blocks1, layer = 2, per = ps.blocks2, ks = ps.ks2;
+        const int c = blk / per, b = blk - c * per;
+        int step, plane;
+        if (b < ks)
+            step = b, plane = sub;
+        else
+            step = 3 * (b - ks) + sub, plane = 0;
+        const int unit = c * AT_NCHUNK + n, k = step * 16 + kc * 8 + k8;
         float v = 0.f;
-        int plane;
-        if (blk < ps.nc * ps.blocks1) {
-            const int sub = e / (AT_SUB / 2), w = e - sub * (AT_SUB / 2);  // piece, element within the piece
-            const int kc = w / 1024, n = (w - kc * 1024) / 8, k8 = w & 7;
-            const int c = blk / ps.blocks1, b = blk - c * ps.blocks1;
-            int step;
-            if (b < ps.ks1)
-                step = b, plane = sub;
+        if (step < ks) {
+            if (layer == 1)
+                v = k < d ? params[nd.oW1() + (int64_t)unit * d + k] : 0.f;
             else
-                step = 3 * (b - ps.ks1) + sub, plane = 0;
-            const int unit = c * AT_NCHUNK + n, k = step * 16 + kc * 8 + k8;
-            if (step < ps.ks1 && k < d) v = params[nd.oW1() + (int64_t)unit * d + k];
-        } else {
-            blk -= ps.nc * ps.blocks1;
-            const int sub = e / 1024, w = e - sub * 1024;  // six 2 KB pieces per block
-            const int kc = w / 512, n = (w - kc * 512) / 8, k8 = w & 7;
-            const int c = blk / ps.blocks2, b = blk - c * ps.blocks2;
-            int step;
-            if (b < ps.ks2 / 2)
-                step = 2 * b + sub / 3, plane = sub % 3;
-            else
-                step = 6 * (b - ps.ks2 / 2) + sub, plane = 0;
-            const int unit = c * AT_NSUB + n, k = step * 16 + kc * 8 + k8;
-            if (step < ps.ks2) v = params[nd.oW2() + (int64_t)unit * H + k];
+                v = params[nd.oW2() + (int64_t)unit * H + k];
         }
         const Trunc3 t = trunc3(v);
         pack[i] = hi16(plane == 0 ? t.t1 : plane == 1 ? t.t2 : t.t3);
@@ -114,8 +101,8 @@ constexpr int OFF_BIAS = OFF_W3V + 4 * 256 * 4;                       // f32 b1 
 constexpr int OFF_B3 = OFF_BIAS + 4 * 256 * 4;                        // f32 [32] policy + [1] value (+ pad)
 constexpr int OFF_COMB = OFF_B3 + 256;                                // f32 [128][33]: the two column halves meet here
 constexpr int OFF_VCOMB = OFF_COMB + AT_M * (AT_MAX_A + 1) * 4;       // f32 [128]
-constexpr int OFF_BAR = OFF_VCOMB + AT_M * 4;                         // mbarriers: full[6] empty[6] acc_full[2] acc_empty[2] a_ready
-constexpr int AT_SMEM_BYTES = OFF_BAR + (2 * AT_STAGES + 5) * 8 + 8;
+constexpr int OFF_BAR = OFF_VCOMB + AT_M * 4;                         // mbarriers: full[6] empty[6] acc_full acc_empty a_ready
+constexpr int AT_SMEM_BYTES = OFF_BAR + (2 * AT_STAGES + 3) * 8 + 8;
 static_assert(AT_SMEM_BYTES <= 227 * 1024, "tensor-core actor kernel exceeds shared memory");
 static_assert(OFF_RING % 128 == 0 && OFF_BAR % 8 == 0, "alignment");
 
@@ -140,7 +127,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
     float *bias_s = reinterpret_cast<float *>(smem + OFF_BIAS), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
     float *comb_s = reinterpret_cast<float *>(smem + OFF_COMB), *vcomb_s = reinterpret_cast<float *>(smem + OFF_VCOMB);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *empty = full + AT_STAGES;
-    uint64_t *acc_full = empty + AT_STAGES, *acc_empty = acc_full + 2, *a_ready = acc_full + 4;  // [2]: accumulator halves
+    uint64_t *acc_full = empty + AT_STAGES, *acc_empty = acc_full + 1, *a_ready = acc_full + 2;
     uint32_t *tmem_s = reinterpret_cast<uint32_t *>(a_ready + 1);
 
     constexpr int NC = H / AT_NCHUNK;
@@ -163,7 +150,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
     if (warp == 0) tmem_alloc(tmem_s, AT_TM_COLS);
     if (tid == 0) {
         for (int s = 0; s < AT_STAGES; ++s) mbar_init(&full[s], 1), mbar_init(&empty[s], 1);
-        for (int x = 0; x < 2; ++x) mbar_init(&acc_full[x], 1), mbar_init(&acc_empty[x], AT_WORKERS / 32);
+        mbar_init(acc_full, 1);
+        mbar_init(acc_empty, AT_WORKERS / 32);
         mbar_init(a_ready, AT_WORKERS / 32);
         mbar_fence_init();
     }
@@ -194,25 +182,32 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         const uint32_t ring_u = smem_u32(ring), obs_u = smem_u32(obs_p);
         // Descriptors are built once per ring block (one move into uniform registers) and stepped by compile-time constants:
         // with a descriptor computed per MMA the issue loop ran at 161 cycles per MMA instead of the tensor core's 64.
-        constexpr uint64_t SUBQ = AT_SUB >> 4, PLQ = OBS_PLANE >> 4, SUB2Q = 2048 >> 4;
-        constexpr uint32_t IDESC2 = idesc_bf16(AT_M, AT_NSUB, false, false);
-        uint32_t st = 0, ph = 0, tcount = 0;
-        uint32_t f0 = 0u, f1 = 0u;  // how often each accumulator half has been filled (mbarrier phases)
+        constexpr uint64_t SUBQ = AT_SUB >> 4, PLQ = OBS_PLANE >> 4;
+        uint32_t st = 0, ph = 0, chunk_n = 0, tcount = 0;
         auto next_stage = [&]() {
             if (++st == AT_STAGES) st = 0, ph ^= 1u;
         };
-        // layer 1, one chunk of 128 units into the whole accumulator: A = observation planes in shared memory
-        auto layer1_chunk = [&](int ks) {
+        auto run_chunk = [&](auto l1_tag, int ks) {
+            constexpr bool L1 = decltype(l1_tag)::value;
             const uint32_t acc_t = tmem + AT_TM_ACC;
             for (int s = 0; s < ks; ++s) {  // cross pass: the five small products of K step s
                 AT_WAIT_FULL(&full[st], ph);
                 const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 2048, 128);
-                const uint64_t ad = smem_desc(obs_u + s * 2 * OBS_CHUNK, OBS_CHUNK, 128);
-                AT_MMA(mma_bf16_elect(acc_t, ad, bd + 2 * SUBQ, IDESC, s > 0));
-                AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd + SUBQ, IDESC, true));
-                AT_MMA(mma_bf16_elect(acc_t, ad + 2 * PLQ, bd, IDESC, true));
-                AT_MMA(mma_bf16_elect(acc_t, ad, bd + SUBQ, IDESC, true));
-                AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd, IDESC, true));
+                if (L1) {
+                    const uint64_t ad = smem_desc(obs_u + s * 2 * OBS_CHUNK, OBS_CHUNK, 128);
+                    AT_MMA(mma_bf16_elect(acc_t, ad, bd + 2 * SUBQ, IDESC, s > 0));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + 2 * PLQ, bd, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_elect(acc_t, ad + PLQ, bd, IDESC, true));
+                } else {
+                    const uint32_t at = tmem + AT_TM_A + 8 * s;
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + 2 * SUBQ, IDESC, s > 0));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 256, bd, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + SUBQ, IDESC, true));
+                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd, IDESC, true));
+                }
                 mma_commit_warp(&empty[st]);
                 next_stage();
             }
@@ -221,66 +216,30 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                 const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 2048, 128);
 #pragma unroll
                 for (int j = 0; j < 3; ++j)
-                    if (s0 + j < ks)
-                        AT_MMA(mma_bf16_elect(acc_t, smem_desc(obs_u + (s0 + j) * 2 * OBS_CHUNK, OBS_CHUNK, 128), bd + j * SUBQ, IDESC, true));
+                    if (s0 + j < ks) {
+                        if (L1)
+                            AT_MMA(mma_bf16_elect(acc_t, smem_desc(obs_u + (s0 + j) * 2 * OBS_CHUNK, OBS_CHUNK, 128), bd + j * SUBQ, IDESC, true));
+                        else
+                            AT_MMA(mma_bf16_ts_elect(acc_t, tmem + AT_TM_A + 8 * (s0 + j), bd + j * SUBQ, IDESC, true));
+                    }
                 mma_commit_warp(&empty[st]);
                 next_stage();
             }
-        };
-        // layer 2, one sub-chunk of 64 units into accumulator half x: A = the h1 planes in tensor memory (measured: 35.5
-        // cycles per N=64 MMA with A in TMEM against 64.1 for N=128 -- two halves in turn cost 11 % more tensor time and
-        // take the TMEM read-out (64 B per cycle: 512 cycles per half) and the hand-off out of the critical path)
-        auto layer2_sub = [&](int x) {
-            constexpr int ks = H / 16;
-            const uint32_t acc_t = tmem + AT_TM_ACC + AT_NSUB * x;
-            for (int b = 0; b < ks / 2; ++b) {  // cross pass: K steps 2b, 2b+1
-                AT_WAIT_FULL(&full[st], ph);
-                const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 1024, 128);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const uint32_t at = tmem + AT_TM_A + 8 * (2 * b + h);
-                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + (3 * h + 2) * SUB2Q, IDESC2, b > 0 || h > 0));
-                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd + (3 * h + 1) * SUB2Q, IDESC2, true));
-                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 256, bd + (3 * h) * SUB2Q, IDESC2, true));
-                    AT_MMA(mma_bf16_ts_elect(acc_t, at, bd + (3 * h + 1) * SUB2Q, IDESC2, true));
-                    AT_MMA(mma_bf16_ts_elect(acc_t, at + 128, bd + (3 * h) * SUB2Q, IDESC2, true));
-                }
-                mma_commit_warp(&empty[st]);
-                next_stage();
-            }
-            for (int s0 = 0; s0 < ks; s0 += 6) {  // main pass: plane 1 x plane 1, six K steps per block
-                AT_WAIT_FULL(&full[st], ph);
-                const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 1024, 128);
-#pragma unroll
-                for (int j = 0; j < 6; ++j)
-                    if (s0 + j < ks) AT_MMA(mma_bf16_ts_elect(acc_t, tmem + AT_TM_A + 8 * (s0 + j), bd + j * SUB2Q, IDESC2, true));
-                mma_commit_warp(&empty[st]);
-                next_stage();
-            }
-        };
-        auto wait_empty = [&](int x) {
-            mbar_wait(&acc_empty[x], ((x ? f1 : f0) & 1u) ^ 1u);  // the epilogue has read the previous contents
         };
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
             mbar_wait(a_ready, tcount & 1u);  // this tile's observation planes are in shared memory
             fence_after_sync();
-            for (int net = 0; net < nets; ++net) {
-                for (int c = 0; c < NC; ++c) {  // layer 1 fills both halves at once
-                    wait_empty(0), wait_empty(1);
-                    fence_after_sync();
-                    layer1_chunk(ps.ks1);
-                    mma_commit_warp(&acc_full[0]), mma_commit_warp(&acc_full[1]);
-                    ++f0, ++f1;
-                }
-                for (int c = 0; c < H / AT_NSUB; ++c) {
-                    const int x = c & 1;
-                    wait_empty(x);
-                    fence_after_sync();
-                    layer2_sub(x);
-                    mma_commit_warp(&acc_full[x]);
-                    if (x) ++f1; else ++f0;
-                }
-            }
+            for (int net = 0; net < nets; ++net)
+                for (int layer = 1; layer <= 2; ++layer)
+                    for (int c = 0; c < NC; ++c, ++chunk_n) {
+                        mbar_wait(acc_empty, (chunk_n & 1u) ^ 1u);  // the epilogue has read the previous chunk
+                        fence_after_sync();
+                        if (layer == 1)
+                            run_chunk(std::true_type{}, ps.ks1);
+                        else
+                            run_chunk(std::false_type{}, H / 16);
+                        mma_commit_warp(acc_full);
+                    }
         }
     } else {
         // ---- the eight worker warps: thread = environment (TMEM lane), column half hf ------------------------------------
@@ -340,21 +299,20 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         };
 
         if ((int64_t)blockIdx.x < tiles) convert_obs(blockIdx.x);
-        uint32_t f0 = 0u, f1 = 0u;  // fills of the two accumulator halves seen so far (mbarrier phases)
+        uint32_t chunk_n = 0;
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             const int64_t grow = tile * AT_M + row;
             const bool valid = grow < a.batch;
             for (int net = 0; net < nets; ++net) {
                 const float *b1 = bias_s + 512 * net, *b2 = b1 + 256;
                 // ---- layer 1: h1 -> the A operand of layer 2 in tensor memory --------------------------------------------
-                for (int c = 0; c < NC; ++c) {
-                    mbar_wait(&acc_full[0], f0 & 1u), mbar_wait(&acc_full[1], f1 & 1u);
-                    ++f0, ++f1;
+                for (int c = 0; c < NC; ++c, ++chunk_n) {
+                    mbar_wait(acc_full, chunk_n & 1u);
                     fence_after_sync();
                     float v[64];
                     load_chunk(v, b1, c);
                     const bool last = c + 1 == NC;
-                    if (!last) arrive(&acc_empty[0]), arrive(&acc_empty[1]);  // the next chunk of layer 1 may overwrite it already
+                    if (!last) arrive(acc_empty);  // the next chunk of layer 1 may overwrite the accumulator already
 #ifndef AT_DBG_NO_EPI
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -372,7 +330,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     if (v[3] == 123.f) vcomb_s[row] = v[5];
 #endif
                     if (last) {
-                        arrive(&acc_empty[0]), arrive(&acc_empty[1]);  // layer 2 reads the planes: only now
+                        arrive(acc_empty);  // layer 2 reads the planes: only now
                         // every MMA that reads the observation planes has retired: the next tile's can be built under layer 2
                         if (net == nets - 1 && tile + gridDim.x < tiles) convert_obs(tile + gridDim.x);
                     }
@@ -383,22 +341,13 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                 for (int i = 0; i < AT_MAX_A; ++i) head[i] = 0.f;
                 const float *w3 = net ? w3v_s : w3pi_s;
                 const int outs4 = net ? 4 : A4;
-                for (int c = 0; c < H / AT_NSUB; ++c) {  // sub-chunks of 64 units, accumulator halves in turn
-                    const int x = c & 1;
-                    mbar_wait(&acc_full[x], (x ? f1 : f0) & 1u);
-                    if (x) ++f1; else ++f0;
+                for (int c = 0; c < NC; ++c, ++chunk_n) {
+                    mbar_wait(acc_full, chunk_n & 1u);
                     fence_after_sync();
-                    float v[32];  // this thread's 32 columns of the half: units 64 c + 32 hf ..
-                    tmem_ld32(tmem_lane + AT_TM_ACC + AT_NSUB * x + 32 * hf, v);
-                    arrive(&acc_empty[x]);  // the values are in registers: the tensor core moves on while the head is summed
-                    const float *bb = b2 + AT_NSUB * c + 32 * hf;
-#pragma unroll
-                    for (int i = 0; i < 32; i += 4) {
-                        const float4 b = *reinterpret_cast<const float4 *>(bb + i);
-                        v[i] = fmaxf(v[i] + b.x, 0.f), v[i + 1] = fmaxf(v[i + 1] + b.y, 0.f);
-                        v[i + 2] = fmaxf(v[i + 2] + b.z, 0.f), v[i + 3] = fmaxf(v[i + 3] + b.w, 0.f);
-                    }
-                    const float *wc = w3 + AT_NSUB * c + 32 * hf;
+                    float v[64];
+                    load_chunk(v, b2, c);
+                    arrive(acc_empty);  // the values are in registers: the tensor core moves on while the head is summed
+                    const float *wc = w3 + AT_NCHUNK * c + 64 * hf;
 #ifdef AT_DBG_NO_EPI
                     head[0] += v[7];
                     if (false)
@@ -407,7 +356,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     for (int a0 = 0; a0 < AT_MAX_A; a0 += 4)
                         if (a0 < outs4) {
 #pragma unroll
-                            for (int i = 0; i < 32; i += 4) {
+                            for (int i = 0; i < 64; i += 4) {
 #pragma unroll
                                 for (int t = 0; t < 4; ++t) {
                                     const float4 w = *reinterpret_cast<const float4 *>(wc + (a0 + t) * H + i);
