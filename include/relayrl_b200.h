@@ -53,6 +53,10 @@ extern "C" {
 /* rrl_config_t.flags.  RRL_FLAG_TC_ANY_SIZE: run the tensor-core learner kernel at every batch size; by default batches
  * under 32 768 transitions take the CUDA-core kernel (csrc/mlp_tc.cu, accuracy note).  For tests and diagnostics. */
 #define RRL_FLAG_TC_ANY_SIZE 1
+/* RRL_FLAG_NO_FUSED_ITERS: on one rank, batches of at most one 64-row tile per SM run all train_vf_iters value steps of an
+ * epoch in one cooperative launch (bit-identical to one launch per step, ~3x less latency at CartPole sizes); this flag
+ * keeps one launch per step.  For tests and diagnostics. */
+#define RRL_FLAG_NO_FUSED_ITERS 2
 
 #define RRL_NCCL_ID_BYTES 128
 

@@ -39,6 +39,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bo
     RRL_TRY(dmalloc(&net.params, P, err));
     net.grad = net.m = net.v = nullptr;
     net.grad64 = nullptr;
+    net.fused_barrier = nullptr;
     net.partials64 = net.loss_partials = net.loss_out = nullptr;
     if (train) {
         RRL_TRY(dmalloc(&net.grad, P, err));
@@ -48,6 +49,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bo
         RRL_TRY(dmalloc(&net.loss_partials, 4 * (size_t)grid, err));
         RRL_TRY(dmalloc(&net.loss_out, 4, err));
         if (data_parallel) RRL_TRY(dmalloc(&net.grad64, P, err));
+        if (!data_parallel) RRL_TRY(dmalloc(&net.fused_barrier, 4, err));
     }
     return RRL_OK;
 }
@@ -55,7 +57,7 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bo
 void net_free(NetState &net)
 {
     cudaFree(net.params), cudaFree(net.grad), cudaFree(net.m), cudaFree(net.v);
-    cudaFree(net.partials64), cudaFree(net.loss_partials), cudaFree(net.loss_out), cudaFree(net.grad64);
+    cudaFree(net.partials64), cudaFree(net.loss_partials), cudaFree(net.loss_out), cudaFree(net.grad64), cudaFree(net.fused_barrier);
     net = NetState{};
 }
 

@@ -68,7 +68,13 @@ int32_t rrl_train_epoch(rrl_learner_t *h, rrl_epoch_stats_t *out)
             RRL_CUDA_OK(cudaMemcpyAsync(h->loss_sync + 3, h->vf.loss_out, sizeof(double), cudaMemcpyDeviceToDevice, st), h->err);
             RRL_CUDA_OK(cudaMemcpyAsync(h->loss_sync + 4, h->vf.loss_out, sizeof(double), cudaMemcpyDeviceToDevice, st), h->err);
         }
-        for (int i = 0; i < c.train_vf_iters; ++i) {
+        // small batch on one rank: all the steps in one cooperative launch, bit-identical to the loop below (mlp.cu)
+        const bool fused = c.train_vf_iters > 0 && !(c.flags & RRL_FLAG_NO_FUSED_ITERS) &&
+                           value_iters_fused_supported(h->vf, tb, c.train_vf_iters, c.nranks);
+        if (fused)
+            RRL_TRY(value_iters_fused_launch(h->vf, tb, c.train_vf_iters, c.vf_lr, c.adam_beta1, c.adam_beta2, c.adam_eps,
+                                             h->loss_sync + 3, h->loss_sync + 4, st, h->err, &h->launches));
+        for (int i = 0; i < (fused ? 0 : c.train_vf_iters); ++i) {
             RRL_TRY(value_pass_launch(h->vf, tb, true, nullptr, st, h->err, &h->launches));
             if (i == 0)  // v_l_old: loss before the first step (REINFORCE.py:103)
                 RRL_CUDA_OK(cudaMemcpyAsync(h->loss_sync + 3, h->vf.loss_out, sizeof(double), cudaMemcpyDeviceToDevice, st), h->err);

@@ -76,6 +76,7 @@ struct NetState {
     NetDims dims;
     float *params;    // flat, torch order
     float *grad;      // flat gradient (after the CTA-partial reduction)
+    unsigned *fused_barrier;  // grid barrier counter of mlp_value_iters_kernel (small batches, single rank)
     double *grad64;   // data parallel only: this rank's float64 gradient sum, all-reduced in float64 and rounded
                       // to f32 once afterwards, so that N ranks and one rank differ by f64 re-association only
     float *m, *v;     // Adam moments
@@ -96,6 +97,10 @@ int32_t policy_pass_launch(NetState &net, const TrainBuffers &tb, int logp_mode,
 int32_t value_pass_launch(NetState &net, const TrainBuffers &tb, bool with_grad, float *v_out,
                           cudaStream_t stream, ErrBuf &err, int *launches);
 // grad (already reduced, and all-reduced across ranks by the caller) -> Adam update of params (+ transposed copies)
+// small batches on one rank: all value iterations of an epoch in one cooperative launch (mlp.cu)
+bool value_iters_fused_supported(const NetState &net, const TrainBuffers &tb, int iters, int nranks);
+int32_t value_iters_fused_launch(NetState &net, const TrainBuffers &tb, int iters, double lr, double b1, double b2, double eps,
+                                 double *loss_first, double *loss_last, cudaStream_t stream, ErrBuf &err, int *launches);
 // grad64 (all-reduced) -> grad, one rounding
 int32_t grad_round_launch(NetState &net, cudaStream_t stream, ErrBuf &err, int *launches);
 int32_t adam_launch(NetState &net, double lr, double b1, double b2, double eps, cudaStream_t stream,

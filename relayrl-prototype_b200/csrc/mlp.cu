@@ -152,13 +152,13 @@ __device__ __forceinline__ void gemm_outer(const float *__restrict__ X_s, int ld
     }
 }
 
+// One pass over this CTA's tiles: the body of mlp_tile_kernel, and of every iteration of mlp_value_iters_kernel.
 template <int H, int MODE, bool GRAD>
-__global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tile_kernel(MlpArgs a)
+__device__ __forceinline__ void mlp_tile_body(const MlpArgs &a, float *smem)
 {
     constexpr int NG = H / 64;
     constexpr int S = MLP_THREADS / H;   // row splits of the column passes
     constexpr int MS = TILE_M / S;       // rows per split
-    extern __shared__ __align__(16) float smem[];
     const int d = a.d, out = a.out;
     const SmemLayout L = smem_layout(d, H, out, GRAD);
     float *W2_s = smem + L.w2, *W1_s = smem + L.w1, *W3_s = smem + L.w3;
@@ -180,16 +180,15 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tile_kernel(MlpArgs a)
         const float *W1 = a.params + nd.oW1(), *W2 = a.params + nd.oW2(), *W3 = a.params + nd.oW3();
         for (int i = tid; i < H * dp; i += MLP_THREADS) {
             const int rj = i / dp, ci = i - rj * dp;
-            W1_s[i] = ci < d ? W1[rj * d + ci] : 0.f;
+            W1_s[i] = ci < d ? __ldcg(&W1[rj * d + ci]) : 0.f;
         }
         for (int i = tid; i < H * (H / 4); i += MLP_THREADS) {
             const int rj = i / (H / 4), c4 = i - rj * (H / 4);
-            *reinterpret_cast<float4 *>(&W2_s[rj * ldh + 4 * c4]) =
-                *reinterpret_cast<const float4 *>(&W2[rj * H + 4 * c4]);
+            *reinterpret_cast<float4 *>(&W2_s[rj * ldh + 4 * c4]) = __ldcg(reinterpret_cast<const float4 *>(&W2[rj * H + 4 * c4]));
         }
-        for (int i = tid; i < out * H; i += MLP_THREADS) W3_s[i] = W3[i];
-        for (int i = tid; i < H; i += MLP_THREADS) b1_s[i] = a.params[nd.ob1() + i], b2_s[i] = a.params[nd.ob2() + i];
-        if (tid < MAX_OUT) b3_s[tid] = tid < out ? a.params[nd.ob3() + tid] : 0.f, db3_s[tid] = 0.f;
+        for (int i = tid; i < out * H; i += MLP_THREADS) W3_s[i] = __ldcg(&W3[i]);
+        for (int i = tid; i < H; i += MLP_THREADS) b1_s[i] = __ldcg(&a.params[nd.ob1() + i]), b2_s[i] = __ldcg(&a.params[nd.ob2() + i]);
+        if (tid < MAX_OUT) b3_s[tid] = tid < out ? __ldcg(&a.params[nd.ob3() + tid]) : 0.f, db3_s[tid] = 0.f;
         if (GRAD) {
             for (int i = tid; i < S * dpad * H; i += MLP_THREADS) dW1_s[i] = 0.f;
             for (int i = tid; i < S * out * H; i += MLP_THREADS) dW3_s[i] = 0.f;
@@ -504,6 +503,78 @@ __global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tile_kernel(MlpArgs a)
     }
 }
 
+template <int H, int MODE, bool GRAD>
+__global__ void __launch_bounds__(MLP_THREADS, 1) mlp_tile_kernel(MlpArgs a)
+{
+    extern __shared__ __align__(16) float smem[];
+    mlp_tile_body<H, MODE, GRAD>(a, smem);
+}
+
+// ---- small batches: all value iterations of an epoch in ONE launch ------------------------------------------------------
+// REINFORCE.train_model runs train_vf_iters (80) Adam steps on the value net per epoch (REINFORCE.py:110-115).  On a
+// CartPole-sized batch (config C1: ~2 000 transitions = 32 tiles) each step is three latency-bound launches -- pass,
+// reduce, Adam: ~64 us, of which the arithmetic is ~12.  Here the CTAs stay resident (cooperative launch, one tile each)
+// and iterate: pass over the own tile (mlp_tile_body, weights re-read through L2) -> grid barrier -> every thread
+// reduces its share of the parameters over the CTAs' float64 partials in the same fixed order as grad_reduce_kernel
+// and applies adam_kernel's operations to them -> grid barrier.  Same arithmetic in the same order as the three-launch
+// path: the weights come out bit-identical (tests/test_gpu_learner.py::test_fused_value_iterations_bit_identical).
+constexpr int FUSED_MAX_ITERS = 256;
+struct FusedArgs {
+    int iters, used;             // Adam steps; CTAs that own a tile (= the grid)
+    float *params, *grad, *m, *v;
+    unsigned *barrier;           // zeroed before the launch
+    double *loss_first, *loss_last;  // sum of squared errors before the first / before the last step
+    float w1, b2, w2, eps;       // 1-beta1, beta2, 1-beta2, eps
+    float bc2_sqrt[FUSED_MAX_ITERS], neg_step[FUSED_MAX_ITERS];  // per step, formed on the host exactly as adam_launch does
+};
+
+__device__ __forceinline__ void grid_barrier(unsigned *ctr, unsigned target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1u);
+        unsigned seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ctr) : "memory");
+        } while (seen < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+template <int H>
+__global__ void __launch_bounds__(MLP_THREADS, 1) mlp_value_iters_kernel(MlpArgs a, const __grid_constant__ FusedArgs f)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int64_t P = a.n_params;
+    const int64_t gtid = (int64_t)blockIdx.x * MLP_THREADS + threadIdx.x, gthreads = (int64_t)gridDim.x * MLP_THREADS;
+    unsigned phase = 0;
+    for (int it = 0; it < f.iters; ++it) {
+        mlp_tile_body<H, MODE_VALUE, true>(a, smem);
+        grid_barrier(f.barrier, ++phase * gridDim.x);
+        // grad_reduce_kernel + adam_kernel on this thread's parameters (partials and weights through L2: other SMs wrote them)
+        for (int64_t p = gtid; p < P; p += gthreads) {
+            double s = 0.0;
+            for (int c = 0; c < f.used; ++c) s += __ldcg(&a.partials[(size_t)c * P + p]);
+            const float gi = (float)s;
+            float mi = f.m[p], vi = f.v[p];
+            mi = __fadd_rn(mi, __fmul_rn(f.w1, __fsub_rn(gi, mi)));
+            vi = __fadd_rn(__fmul_rn(vi, f.b2), __fmul_rn(__fmul_rn(f.w2, gi), gi));
+            const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), f.bc2_sqrt[it]), f.eps);
+            __stcg(&f.params[p], __fadd_rn(__ldcg(&f.params[p]), __fdiv_rn(__fmul_rn(f.neg_step[it], mi), denom)));
+            f.m[p] = mi, f.v[p] = vi, f.grad[p] = gi;
+        }
+        if (gtid == 0 && (it == 0 || it == f.iters - 1)) {
+            double s = 0.0;
+            for (int c = 0; c < f.used; ++c) s += __ldcg(&a.loss_partials[(size_t)c * 4]);
+            if (it == 0) *f.loss_first = s;
+            if (it == f.iters - 1) *f.loss_last = s;
+        }
+        grid_barrier(f.barrier, ++phase * gridDim.x);
+    }
+}
+
 // grad[p] = sum over CTAs of the float64 partials, fixed order; losses likewise.
 __global__ void __launch_bounds__(256) grad_reduce_kernel(const double *__restrict__ partials, int grid_used,
                                                          int64_t n_params, float *__restrict__ grad,
@@ -657,6 +728,47 @@ int32_t value_pass_launch(NetState &net, const TrainBuffers &tb, bool with_grad,
                           ErrBuf &err, int *launches)
 {
     return run_pass(net, tb, MODE_VALUE, with_grad, v_out, stream, err, launches);
+}
+
+bool value_iters_fused_supported(const NetState &net, const TrainBuffers &tb, int iters, int nranks)
+{
+    const NetDims &nd = net.dims;
+    const int64_t tiles = (tb.n + TILE_M - 1) / TILE_M;
+    return nranks <= 1 && iters >= 1 && iters <= FUSED_MAX_ITERS && (nd.H == 64 || nd.H == 128) && tiles >= 1 && tiles <= net.grid &&
+           net.fused_barrier != nullptr && !tc_pass_supported(nd, MODE_VALUE, true, tb.tc_any_size ? (int64_t)1 << 40 : tb.n);
+}
+
+// train_vf_iters value steps in one cooperative launch (see mlp_value_iters_kernel); loss_first / loss_last: device doubles
+int32_t value_iters_fused_launch(NetState &net, const TrainBuffers &tb, int iters, double lr, double b1, double b2, double eps,
+                                 double *loss_first, double *loss_last, cudaStream_t stream, ErrBuf &err, int *launches)
+{
+    const NetDims &nd = net.dims;
+    RRL_TRY(mlp_check_dims(nd.d, nd.H, nd.out, err));
+    MlpArgs a;
+    a.params = net.params, a.d = nd.d, a.out = nd.out;
+    a.obs = tb.obs, a.act = tb.act, a.mask = tb.mask, a.adv = tb.adv, a.ret = tb.ret, a.logp_old = tb.logp_old;
+    a.stats = tb.stats, a.n = tb.n;
+    a.inv_n = 1.0f / (float)tb.n_global;
+    a.partials = net.partials64, a.loss_partials = net.loss_partials, a.n_params = nd.n_params(), a.out_rows = nullptr;
+    FusedArgs f;
+    f.iters = iters, f.used = (int)((tb.n + TILE_M - 1) / TILE_M);
+    f.params = net.params, f.grad = net.grad, f.m = net.m, f.v = net.v, f.barrier = net.fused_barrier;
+    f.loss_first = loss_first, f.loss_last = loss_last;
+    f.w1 = (float)(1.0 - b1), f.b2 = (float)b2, f.w2 = (float)(1.0 - b2), f.eps = (float)eps;
+    for (int i = 0; i < iters; ++i) {  // exactly adam_launch's scalars for steps net.step + 1 .. net.step + iters
+        const double t = (double)(net.step + 1 + i);
+        const double bc1 = 1.0 - pow(b1, t), bc2 = 1.0 - pow(b2, t);
+        f.bc2_sqrt[i] = (float)sqrt(bc2), f.neg_step[i] = (float)(-(lr / bc1));
+    }
+    const size_t smem = mlp_smem_bytes(nd.d, nd.H, nd.out);
+    RRL_CUDA_OK(cudaMemsetAsync(net.fused_barrier, 0, sizeof(unsigned), stream), err);
+    void *args[2] = {&a, &f};
+    const void *fn = nd.H == 64 ? (const void *)mlp_value_iters_kernel<64> : (const void *)mlp_value_iters_kernel<128>;
+    RRL_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
+    RRL_CUDA_OK(cudaLaunchCooperativeKernel(fn, dim3((unsigned)f.used), dim3(MLP_THREADS), args, smem, stream), err);
+    net.step += iters;
+    if (launches) *launches += 1;
+    return RRL_OK;
 }
 
 int32_t grad_round_launch(NetState &net, cudaStream_t stream, ErrBuf &err, int *launches)

@@ -14,6 +14,7 @@ RRL_OK = 0
 RRL_F32, RRL_F64 = 0, 1
 RRL_LOGP_REFERENCE, RRL_LOGP_LOG_SOFTMAX = 0, 1
 RRL_FLAG_TC_ANY_SIZE = 1
+RRL_FLAG_NO_FUSED_ITERS = 2
 NCCL_ID_BYTES = 128
 
 

@@ -49,6 +49,10 @@ def assert_weights_close(actual, desired, lr, learner=None, which=None, excused=
         sv = np.sqrt(v / (1.0 - 0.999 ** step))
         cond = min(step, 80) * 3e-7 * sv.max() / (sv + 1e-8)
         over = err > W_RTOL * np.abs(desired) + lr * np.maximum(0.02, cond)
+        if excused:        # outliers of earlier epochs keep their offset while v_hat grows: they stay within a tenth of a step
+            ex = np.fromiter(excused, dtype=np.int64)
+            assert (err[ex] <= 0.1 * lr).all(), "an earlier outlier grew beyond 0.1 lr: %s" % (err[ex] / lr)
+            over[ex] = False
         assert not over.any(), "parameter %d is off by %.3g lr with sqrt(v_hat) = %.3g (max %.3g): more than 0.02 lr and " \
             "more than its conditioning explains (%.3g lr)" % (int(np.argmax(over)), err[np.argmax(over)] / lr,
                                                               sv[np.argmax(over)], sv.max(), cond[np.argmax(over)])
@@ -415,3 +419,43 @@ def test_pickle_ingest_matches_golden_epoch_and_is_all_or_nothing():
     np.testing.assert_allclose(L.returns(n), g[p + "ret_raw"], rtol=1e-6, atol=1e-6)
     np.testing.assert_allclose(L.advantages(n, normalised=False), g[p + "adv_raw"], rtol=1e-6, atol=1e-6)
     L.close()
+
+
+@pytest.mark.parametrize("H,n,iters", [(128, 2044, 80), (64, 2044, 80), (128, 40, 5), (128, 64 * 148, 7), (64, 64 * 100 + 1, 3)])
+def test_fused_value_iterations_bit_identical(H, n, iters):
+    """Small batches on one rank run all value steps of an epoch in ONE cooperative launch (csrc/mlp.cu,
+    mlp_value_iters_kernel): the same kernels' arithmetic in the same order, so weights, Adam state and losses must equal
+    the one-launch-per-step path bit for bit -- over two epochs (the second starts from step > 0 and a stale tail)."""
+    from relayrl_b200 import Learner, _lib
+    d, A = 4, 2
+    rng = np.random.default_rng(H + n)
+    out = []
+    eps = []
+    for _ in range(2):
+        lens = rng.integers(1, 300, 400)
+        lens = lens[np.cumsum(lens) <= n]
+        if lens.sum() < n:
+            lens = np.append(lens, n - lens.sum())
+        done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
+        m = len(done)
+        eps.append((rng.standard_normal((m, d)), rng.integers(0, A, m).astype(np.float32), np.ones((m, A)),
+                    rng.uniform(-1, 1, m).astype(np.float32), rng.standard_normal(m).astype(np.float32),
+                    rng.standard_normal(m).astype(np.float32), done))
+    for flags in (0, _lib.RRL_FLAG_NO_FUSED_ITERS):
+        L = Learner(d, A, n + 1, hidden=H, with_baseline=True, train_vf_iters=iters, flags=flags)
+        L.set_params(0, lo.flatten(lo.init_params(d, H, A, 1)).numpy())
+        L.set_params(1, lo.flatten(lo.init_params(d, H, 1, 2)).numpy())
+        res = []
+        for e in eps:
+            L.ingest(*e)
+            st = L.train_epoch()
+            res.append((st["loss_v"], st["loss_v_old"], st["loss_pi"], st["kernel_launches"]))
+        res.append((L.get_params(0), L.get_params(1)) + tuple(L.get_opt_state(1)))
+        out.append(res)
+        L.close()
+    fused, plain = out
+    for a, b in zip(fused[:2], plain[:2]):
+        assert a[:3] == b[:3], (a, b)
+        assert a[3] < b[3] and b[3] - a[3] == 3 * iters - 1          # one launch instead of (pass + reduce + Adam) x iters
+    for a, b in zip(fused[2], plain[2]):
+        assert np.array_equal(np.asarray(a), np.asarray(b))
