@@ -49,7 +49,10 @@ int32_t net_alloc(NetState &net, int d, int H, int out, int grid, bool train, bo
         RRL_TRY(dmalloc(&net.loss_partials, 4 * (size_t)grid, err));
         RRL_TRY(dmalloc(&net.loss_out, 4, err));
         if (data_parallel) RRL_TRY(dmalloc(&net.grad64, P, err));
-        if (!data_parallel) RRL_TRY(dmalloc(&net.fused_barrier, 4, err));
+        int dev = 0, coop = 0;
+        if (!data_parallel && cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && coop)
+            RRL_TRY(dmalloc(&net.fused_barrier, 4, err));  // (without cooperative launch the fused small-batch path stays off)
     }
     return RRL_OK;
 }
