@@ -293,7 +293,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             mbar_wait(go1, (uint32_t)(kk & 1));
             TCT(3);
             fence_after_sync();
+#ifdef TC_DBG_SKIP_G1  // timing experiment only (make tc_variants; wrong results): one MMA instead of 48
+            mma_bf16_elect(tmem + TM_D1 + 64 * (kk & 1), smem_desc(W2_k.base, W2_k.lbo, W2_k.sbo), smem_desc(H1_k.base, H1_k.lbo, H1_k.sbo), ID_G1, false);
+#else
             issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1 + 64 * (kk & 1), W2_k, H1_k, ID_G1, false);
+#endif
             mma_commit_warp(bar1);
             TCT(4);
         };
@@ -309,7 +313,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             issue_gemm_bf16x3_ts_warp<TILE_M / 16>(tmem + TM_DW2, hT, hT + 32, tmem + TM_P2, DZ_k, ID_G3, false);
             mma_commit_warp(bar3);
             TCT(1);
+#ifdef TC_DBG_SKIP_G2
+            mma_bf16_elect(tmem + TM_D2, smem_desc(W2_mn.base, W2_mn.lbo, W2_mn.sbo), smem_desc(DZ_mn.base, DZ_mn.lbo, DZ_mn.sbo), ID_G2, false);
+#else
             issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D2, W2_mn, DZ_mn, ID_G2, false);
+#endif
             mma_commit_warp(bar2);
             TCT(2);
         }
