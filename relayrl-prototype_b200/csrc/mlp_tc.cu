@@ -32,9 +32,8 @@ constexpr int TC_H = 128;
 constexpr int TC_MAX_D = 8;
 constexpr int TC_MAX_OUT = 4;
 constexpr int W_PLANE = tc::x_plane_bytes(TC_H, TC_H);    // bytes of one bf16 plane of W2
-constexpr int X_PLANE = tc::x_plane_bytes(TILE_M, TC_H);  // bytes of one bf16 plane of a 64-row activation tile
-constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H), X_CHUNK = tc::x_chunk_bytes(TILE_M);
-// dZ2 is kept transposed: X layout of [unit][row], so that the thread that owns a unit stores 8 rows per 16 bytes
+constexpr int W_CHUNK = tc::x_chunk_bytes(TC_H);
+// H1 and dZ2 are kept transposed: X layout of [unit][row], so that the thread that owns a unit stores 8 rows per 16 bytes
 constexpr int DZ_PLANE = tc::x_plane_bytes(TC_H, TILE_M), DZ_CHUNK = tc::x_chunk_bytes(TC_H);
 // TMEM columns: D1[2] (64 each; after epilogue 1 has read it, D1[k&1] is reused for planes 0 and 1 of H1^T, G3's A
 // operand), plane 2 of H1^T (32), D2 (64), dW2^T (128, one tile), ACC (128, the window's dW2^T sum)
@@ -53,7 +52,8 @@ constexpr int TC_FLUSH = 2 * FLUSH_TILES;
 // and the factor then costs the golden epoch its 1e-5 agreement.  Hence TC_MIN_ROWS: batches too small to fill the
 // pipeline anyway (where the effect is visible) take the CUDA-core kernel, whose float32 FMAs round to nearest.
 constexpr int64_t TC_MIN_ROWS = 32768;  // ~3.5 tiles per SM; below it the CUDA-core kernel runs (see the note above)
-constexpr int NBUF = 4;  // input buffers: tile k-1 (epilogue 2), k (epilogue 1), k+1 (stage 1), k+2 (in flight)
+constexpr int NBUF = 5;  // input buffers: tile k-1 (epilogue 2, which runs on into the next iteration), k (epilogue 1), k+1 (stage 1),
+                         // k+2 (landed), k+3 (in flight from the top of the next iteration)
 constexpr int TC_THREADS = 512;            // 16 worker warps: TMEM lane quarter q = warp & 3, row group rq = warp >> 2
 // + one warp that only issues the MMAs (the issuing thread is held until its MMAs retire: the queue is a few
 // entries deep).  17 warps are allocated as 20, i.e. 96 registers per thread: the dW2 sums therefore live in
@@ -65,7 +65,7 @@ constexpr int TC_RPT = TILE_M / TC_RG;     // rows per thread in the epilogues (
 // shared-memory map (bytes)
 constexpr int OFF_W2 = 0;
 constexpr int OFF_H1 = OFF_W2 + 3 * W_PLANE;
-constexpr int OFF_DZ = OFF_H1 + 3 * X_PLANE;
+constexpr int OFF_DZ = OFF_H1 + 3 * DZ_PLANE;  // (H1 is kept transposed like dZ2: [unit][row])
 constexpr int OFF_OBS = OFF_DZ + 3 * DZ_PLANE;                // f32 [NBUF][64][8]
 constexpr int OFF_W1 = OFF_OBS + NBUF * TILE_M * TC_MAX_D * 4;  // f32 [128][8]
 constexpr int OFF_B1 = OFF_W1 + TC_H * TC_MAX_D * 4;          // f32 [128]
@@ -179,14 +179,15 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
     W2_k.base = W2_mn.base = smem_u32(w2_p), W2_k.plane_bytes = W2_mn.plane_bytes = W_PLANE;
     W2_k.lbo = W_CHUNK, W2_k.sbo = 128, W2_k.kstep = 2 * W_CHUNK;
     W2_mn.sbo = W_CHUNK, W2_mn.lbo = 128, W2_mn.kstep = 256;
-    H1_k.base = H1_mn.base = smem_u32(h1_p), H1_k.plane_bytes = H1_mn.plane_bytes = X_PLANE;
-    H1_k.lbo = X_CHUNK, H1_k.sbo = 128, H1_k.kstep = 2 * X_CHUNK;
-    H1_mn.sbo = X_CHUNK, H1_mn.lbo = 128, H1_mn.kstep = 256;
+    // H1^T [unit][row]: MN-major as G1's B (N = row, K = unit) -- the same view dZ2^T has as G2's B
+    H1_k.base = H1_mn.base = smem_u32(h1_p), H1_k.plane_bytes = H1_mn.plane_bytes = DZ_PLANE;
+    H1_k.lbo = DZ_CHUNK, H1_k.sbo = 128, H1_k.kstep = 2 * DZ_CHUNK;
+    H1_mn.sbo = DZ_CHUNK, H1_mn.lbo = 128, H1_mn.kstep = 256;
     // dZ2^T [unit][row]: K-major as G3's A (M = unit, K = row), MN-major as G2's B (N = row, K = unit)
     DZ_k.base = DZ_mn.base = smem_u32(dz_p), DZ_k.plane_bytes = DZ_mn.plane_bytes = DZ_PLANE;
     DZ_k.lbo = DZ_CHUNK, DZ_k.sbo = 128, DZ_k.kstep = 2 * DZ_CHUNK;
     DZ_mn.sbo = DZ_CHUNK, DZ_mn.lbo = 128, DZ_mn.kstep = 256;
-    constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, false), ID_G2 = idesc_bf16(128, 64, true, true),
+    constexpr uint32_t ID_G1 = idesc_bf16(128, 64, false, true), ID_G2 = idesc_bf16(128, 64, true, true),
                        ID_G3 = idesc_bf16(128, 128, false, false);
 
     // thread-local gradient accumulators for hidden unit j over this thread's quarter of the rows.
@@ -236,50 +237,45 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     auto inputs_landed = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
-    // H1 = relu(obs W1^T + b1) as three bf16 planes (16-byte pieces: one row, 8 units)
-    auto stage1 = [&](int b) {
-        static_assert(TC_THREADS / 32 == TC_H / 8 && TILE_M == 64, "one warp per chunk of 8 hidden units, two rows per lane");
+    // H1 of 16 rows for the hidden unit this thread owns, as bf16x3 words (two rows per word) + the relu bit mask.  Used
+    // twice per tile with the same thread mapping and operation order, so both copies of H1 are identical: by stage 1
+    // (-> shared-memory planes, G1's B operand) and by epilogue 1 (-> tensor memory, G3's A operand).
+    auto h1_words = [&](int b, uint32_t (&hk)[3][TC_RPT / 2], uint32_t &hbits) {
         const float *ob = obs_s + b * TILE_M * TC_MAX_D;
-        const int ch = warp;  // this warp's 8 hidden units; lane <-> rows lane and lane + 32 (W1 is loaded once for both)
-        float4 x[2][D4];
+        float4 w1r[D4];
 #pragma unroll
-        for (int rr = 0; rr < 2; ++rr)
+        for (int i4 = 0; i4 < D4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
+        const float b1 = b1_s[j];
+        hbits = 0u;
 #pragma unroll
-            for (int i4 = 0; i4 < D4; ++i4)
-                x[rr][i4] = *reinterpret_cast<const float4 *>(&ob[(lane + 32 * rr) * TC_MAX_D + 4 * i4]);
-        const float4 ba = *reinterpret_cast<const float4 *>(&b1_s[8 * ch]), bb = *reinterpret_cast<const float4 *>(&b1_s[8 * ch + 4]);
-        const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-        uint32_t p1[2][4], p2[2][4], p3[2][4];
-#pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-            Trunc3 s[2][2];
+        for (int c = 0; c < TC_RPT; c += 2) {
+            Trunc3 s2[2];
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
-                const int u = 8 * ch + e + t;
-                float acc[2] = {bias[e + t], bias[e + t]};
+                const int m = TC_RPT * rq + c + t;
+                float acc = b1;
 #pragma unroll
-                for (int i4 = 0; i4 < D4; ++i4) {  // W1 rows are zero padded
-                        const float4 w = *reinterpret_cast<const float4 *>(&w1_s[u * TC_MAX_D + 4 * i4]);
-#pragma unroll
-                        for (int rr = 0; rr < 2; ++rr) {
-                            acc[rr] = fmaf(x[rr][i4].x, w.x, acc[rr]), acc[rr] = fmaf(x[rr][i4].y, w.y, acc[rr]);
-                            acc[rr] = fmaf(x[rr][i4].z, w.z, acc[rr]), acc[rr] = fmaf(x[rr][i4].w, w.w, acc[rr]);
-                        }
-                    }
-#pragma unroll
-                for (int rr = 0; rr < 2; ++rr) s[rr][t] = trunc3(fmaxf(acc[rr], 0.f));
+                for (int i4 = 0; i4 < D4; ++i4) {  // the observation row is one broadcast load for the whole warp
+                    const float4 x = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
+                    acc = fmaf(x.x, w1r[i4].x, acc), acc = fmaf(x.y, w1r[i4].y, acc);
+                    acc = fmaf(x.z, w1r[i4].z, acc), acc = fmaf(x.w, w1r[i4].w, acc);
+                }
+                hbits |= (acc > 0.f ? 1u : 0u) << (c + t);
+                s2[t] = trunc3(fmaxf(acc, 0.f));
             }
-#pragma unroll
-            for (int rr = 0; rr < 2; ++rr)
-                p1[rr][e >> 1] = pack_hi16(s[rr][0].t1, s[rr][1].t1), p2[rr][e >> 1] = pack_hi16(s[rr][0].t2, s[rr][1].t2),
-                p3[rr][e >> 1] = pack_hi16(s[rr][0].t3, s[rr][1].t3);
+            hk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), hk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2),
+            hk[2][c >> 1] = pack_hi16(s2[0].t3, s2[1].t3);
         }
+    };
+    // stage 1: H1^T planes ([unit][row], like dZ2: the owner of a unit stores 8 rows per 16 bytes)
+    auto stage1 = [&](int b) {
+        uint32_t hk[3][TC_RPT / 2], hbits;
+        h1_words(b, hk, hbits);
 #pragma unroll
-        for (int rr = 0; rr < 2; ++rr) {
-            const int o = ch * X_CHUNK + (lane + 32 * rr) * 16;
-            *reinterpret_cast<uint4 *>(h1_p + o) = make_uint4(p1[rr][0], p1[rr][1], p1[rr][2], p1[rr][3]);
-            *reinterpret_cast<uint4 *>(h1_p + X_PLANE + o) = make_uint4(p2[rr][0], p2[rr][1], p2[rr][2], p2[rr][3]);
-            *reinterpret_cast<uint4 *>(h1_p + 2 * X_PLANE + o) = make_uint4(p3[rr][0], p3[rr][1], p3[rr][2], p3[rr][3]);
+        for (int pl = 0; pl < 3; ++pl) {
+            unsigned char *dst = h1_p + pl * DZ_PLANE + (2 * rq) * DZ_CHUNK + j * 16;  // rows 16 rq .. +7, then +8 .. +15
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(hk[pl][0], hk[pl][1], hk[pl][2], hk[pl][3]);
+            *reinterpret_cast<uint4 *>(dst + DZ_CHUNK) = make_uint4(hk[pl][4], hk[pl][5], hk[pl][6], hk[pl][7]);
         }
     };
     // the 16 worker warps meet at a named barrier; the MMA warp never joins it
@@ -294,9 +290,9 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             TCT(3);
             fence_after_sync();
 #ifdef TC_DBG_SKIP_G1  // timing experiment only (make tc_variants; wrong results): one MMA instead of 48
-            mma_bf16_elect(tmem + TM_D1 + 64 * (kk & 1), smem_desc(W2_k.base, W2_k.lbo, W2_k.sbo), smem_desc(H1_k.base, H1_k.lbo, H1_k.sbo), ID_G1, false);
+            mma_bf16_elect(tmem + TM_D1 + 64 * (kk & 1), smem_desc(W2_k.base, W2_k.lbo, W2_k.sbo), smem_desc(H1_mn.base, H1_mn.lbo, H1_mn.sbo), ID_G1, false);
 #else
-            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1 + 64 * (kk & 1), W2_k, H1_k, ID_G1, false);
+            issue_gemm_bf16x3_warp<TC_H / 16>(tmem + TM_D1 + 64 * (kk & 1), W2_k, H1_mn, ID_G1, false);
 #endif
             mma_commit_warp(bar1);
             TCT(4);
@@ -325,12 +321,16 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 
     uint32_t hb_carry = 0u;
     // ---- epilogue 2 of tile kk (inputs in buffer b3): dz1 = D2 [h1 > 0]; dW1, db1 ------------------------------
-    auto epilogue2 = [&](int kk, int b3) {
+    // (split in two: the accumulator read-out, which must precede the hand-off that lets G2 of the NEXT tile overwrite D2,
+    //  and the arithmetic, which runs after that hand-off, under the next tile's G3 and G2 -- with epilogue 2 as a whole
+    //  ahead of epilogue 1 the workers waited 10 % of every tile for G2 to retire, measured with the timing variants)
+    auto epilogue2_wait = [&](int kk) {
         mbar_wait(bar2, (uint32_t)(kk & 1));
         fence_after_sync();
-        float dh[TC_RPT];
-        tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh);
-        const uint32_t hb = hb_carry;  // bit c: h1 > 0 for row 16 rq + c of that tile (set by this thread in its epilogue 1)
+    };
+    auto epilogue2_load = [&](float (&dh)[TC_RPT]) { tmem_ld16(tmem_lane + TM_D2 + TC_RPT * rq, dh); };
+    // hb: bit c = h1 > 0 for row 16 rq + c of that tile (set by this thread in its epilogue 1)
+    auto epilogue2_math = [&](int b3, const float (&dh)[TC_RPT], uint32_t hb) {
         const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
         float dbl = 0.f;
 #pragma unroll
@@ -340,13 +340,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             dbl += dz1;
 #pragma unroll
             for (int i4 = 0; i4 < D4; ++i4) {
-                {
-                    const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
-                    dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
-                    dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
-                    dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
-                    dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
-                }
+                const float4 t = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
+                dW1acc[4 * i4] = fmaf(dz1, t.x, dW1acc[4 * i4]);
+                dW1acc[4 * i4 + 1] = fmaf(dz1, t.y, dW1acc[4 * i4 + 1]);
+                dW1acc[4 * i4 + 2] = fmaf(dz1, t.z, dW1acc[4 * i4 + 2]);
+                dW1acc[4 * i4 + 3] = fmaf(dz1, t.w, dW1acc[4 * i4 + 3]);
             }
         }
         db1acc += dbl;
@@ -469,13 +467,16 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
         }
         TCT(8);
 
-        // ---- [D] the previous tile's tail: its G3 and G2 retired long ago -----------------------------------------
+        // ---- [D] the previous tile's dW2 (its G3 retired long ago); every TC_FLUSH tiles the spill (the per-unit sums of
+        //      epilogue 2 lag one tile behind: they join the next window) --------------------------------------------------
+        const uint32_t hb_prev = hb_carry;  // tile k-1's relu mask, for its epilogue 2 at the end of this iteration
         if (k > 0) {
             drain(k - 1);
             TCT(7);
-            epilogue2(k - 1, pb3);
-            TCT(10);
-            if (k % TC_FLUSH == 0) spill();
+            if (k % TC_FLUSH == 0) {
+                epilogue2_wait(k - 1);  // the spill stages in the dZ2 planes: G2 of tile k-1 must have read them
+                spill();
+            }
             TCT(11);
         }
 
@@ -497,34 +498,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             fence_before_sync();
             worker_sync();  // (also: every warp has read D1[k & 1])
             fence_after_sync();
-            // H1^T of this tile -> tensor memory (G3's A operand): recomputed from obs with thread = hidden unit, two rows
-            // per 32-bit column; planes 0 and 1 go where D1[k & 1] was, plane 2 has its own 32 columns
+            // H1^T of this tile -> tensor memory (G3's A operand): recomputed exactly as stage 1 did; planes 0 and 1 go where
+            // D1[k & 1] was, plane 2 has its own 32 columns
             {
-                const float *ob = obs_s + b3 * TILE_M * TC_MAX_D;
-                float4 w1r[D4];
-#pragma unroll
-                for (int i4 = 0; i4 < D4; ++i4) w1r[i4] = *reinterpret_cast<const float4 *>(&w1_s[j * TC_MAX_D + 4 * i4]);
-                const float b1 = b1_s[j];
-                uint32_t hk[3][TC_RPT / 2], hbits = 0u;
-#pragma unroll
-                for (int c = 0; c < TC_RPT; c += 2) {
-                    Trunc3 s2[2];
-#pragma unroll
-                    for (int t = 0; t < 2; ++t) {
-                        const int m = TC_RPT * rq + c + t;
-                        float acc = b1;
-#pragma unroll
-                        for (int i4 = 0; i4 < D4; ++i4) {  // same operation order as stage 1: the two copies of H1 are identical
-                                const float4 x = *reinterpret_cast<const float4 *>(&ob[m * TC_MAX_D + 4 * i4]);
-                                acc = fmaf(x.x, w1r[i4].x, acc), acc = fmaf(x.y, w1r[i4].y, acc);
-                                acc = fmaf(x.z, w1r[i4].z, acc), acc = fmaf(x.w, w1r[i4].w, acc);
-                            }
-                        hbits |= (acc > 0.f ? 1u : 0u) << (c + t);
-                        s2[t] = trunc3(fmaxf(acc, 0.f));
-                    }
-                    hk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), hk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2),
-                    hk[2][c >> 1] = pack_hi16(s2[0].t3, s2[1].t3);
-                }
+                uint32_t hk[3][TC_RPT / 2], hbits;
+                h1_words(b3, hk, hbits);
                 const uint32_t hT = tmem_lane + TM_D1 + 64 * (k & 1) + (TC_RPT / 2) * rq;
                 tmem_st8(hT, hk[0]);
                 tmem_st8(hT + 32, hk[1]);
@@ -611,6 +589,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 }
                 pk[0][c >> 1] = pack_hi16(s2[0].t1, s2[1].t1), pk[1][c >> 1] = pack_hi16(s2[0].t2, s2[1].t2), pk[2][c >> 1] = pack_hi16(s2[0].t3, s2[1].t3);
             }
+            if (k > 0) epilogue2_wait(k - 1);  // G2 of tile k-1 has read the dZ2 planes (retired long ago by now) and D2 is complete
 #pragma unroll
             for (int pl = 0; pl < 3; ++pl) {
                 unsigned char *dst = dz_p + pl * DZ_PLANE + (2 * rq) * DZ_CHUNK + j * 16;  // rows 16 rq .. +7, then +8 .. +15
@@ -619,17 +598,25 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
             }
             db2acc += dbl;
         }
+        float dh_prev[TC_RPT];  // D2 of tile k-1, read out before G2 of this tile may overwrite it
+        if (k > 0) epilogue2_load(dh_prev);
         inputs_landed();  // tile k+2's inputs (fetched a whole iteration ago) become visible with the barrier below
         fence_smem_to_async();
         fence_before_sync();
         worker_sync();
         if (tid == 0) mbar_arrive(go23);  // the MMA warp issues G3, then G2
         TCT(6);
+        // ---- epilogue 2 of the previous tile, under this tile's G3 and G2 ---------------------------------------------
+        if (k > 0) epilogue2_math(pb3, dh_prev, hb_prev);
+        TCT(10);
     }
     // ---- pipeline tail: the last tile's drain, epilogue 2 and the final spill ------------------------------------
     if (k > 0) {
         drain(k - 1);
-        epilogue2(k - 1, (k - 1) % NBUF);
+        epilogue2_wait(k - 1);
+        float dh_last[TC_RPT];
+        epilogue2_load(dh_last);
+        epilogue2_math((k - 1) % NBUF, dh_last, hb_carry);
         spill();
     }
     }  // worker warps
