@@ -459,3 +459,38 @@ def test_fused_value_iterations_bit_identical(H, n, iters):
         assert a[3] < b[3] and b[3] - a[3] == 3 * iters - 1          # one launch instead of (pass + reduce + Adam) x iters
     for a, b in zip(fused[2], plain[2]):
         assert np.array_equal(np.asarray(a), np.asarray(b))
+
+
+def test_host_alloc_pinned_view_ingest():
+    """rrl_host_alloc / rrl_host_free: pinned host memory for the caller's packed columns (the e2e leg of bench.py uses
+    torch's pinned tensors; a Rust or C host would use these).  A view over such memory ingests exactly like numpy arrays,
+    with f64 obs/mask on the wire (Q11)."""
+    import ctypes as C
+    from relayrl_b200 import Learner, _lib, host_alloc, host_free
+    from relayrl_b200._lib import BatchView
+    d, A, n = 4, 2, 3000
+    rng = np.random.default_rng(7)
+    lens = [700, 1, 1299, 1000]
+    done = np.concatenate([np.r_[np.zeros(k, np.uint8), np.uint8(1)] for k in lens])
+    m = len(done)
+    cols = dict(obs=rng.standard_normal((m, d)), act=rng.integers(0, A, m).astype(np.float32), mask=np.ones((m, A)),
+                rew=rng.uniform(-1, 1, m).astype(np.float32), val=rng.standard_normal(m).astype(np.float32),
+                logp=rng.standard_normal(m).astype(np.float32), done=done)
+    ptrs = {}
+    for k, arr in cols.items():
+        arr = np.ascontiguousarray(arr)
+        p = host_alloc(arr.nbytes)
+        C.memmove(p, arr.ctypes.data, arr.nbytes)
+        ptrs[k] = p
+    view = BatchView(ptrs["obs"].value, ptrs["act"].value, ptrs["mask"].value, ptrs["rew"].value, ptrs["val"].value,
+                     ptrs["logp"].value, ptrs["done"].value, m, _lib.RRL_F64, _lib.RRL_F64)
+    a, b = Learner(d, A, n + 1, hidden=64, with_baseline=True), Learner(d, A, n + 1, hidden=64, with_baseline=True)
+    a.ingest_raw(view)
+    b.ingest(cols["obs"], cols["act"], cols["mask"], cols["rew"], cols["val"], cols["logp"], cols["done"])
+    (na, ea), (nb, eb) = a.finish(), b.finish()
+    assert (na, ea) == (nb, eb) == (n, len(lens))
+    assert np.array_equal(a.offsets(), b.offsets())
+    assert np.array_equal(a.returns(n), b.returns(n)) and np.array_equal(a.advantages(n, False), b.advantages(n, False))
+    for p in ptrs.values():
+        host_free(p)
+    a.close(), b.close()
