@@ -44,16 +44,47 @@ struct PVal {
     PVal() : i(0) {}
 };
 
+// Containers do not own heap memory: their elements live in two arenas of the graph (one malloc per action was the cost
+// of the first version: 25 containers per action).  A container that grows while it is not the last thing in its arena is
+// moved to the end first; pickle builds containers in batches, so that is rare.
 struct Node {
-    std::vector<PVal> items;     // list / tuple elements, or dict key, value, key, value, ...
-    std::vector<uint8_t> bytes;  // a list that so far holds only integers 0..255 (a Vec<u8> under serde's default)
+    uint32_t start = 0, len = 0;    // list / tuple elements, or dict key, value, key, value, ... : Graph::pool[start .. start+len)
+    uint32_t bstart = 0, blen = 0;  // a list that so far holds only integers 0..255 (a Vec<u8> under serde's default): Graph::bytes
     bool all_bytes = true;
 };
 
 struct Graph {
     std::vector<Node> nodes;
+    std::vector<PVal> pool;
+    std::vector<uint8_t> bytes;
     std::vector<PVal> stack, memo;
     PVal top;
+    const PVal *items(const Node &n) const { return pool.data() + n.start; }
+    const uint8_t *byte_data(const Node &n) const { return bytes.data() + n.bstart; }
+    void push_item(Node &n, const PVal &v)
+    {
+        if ((size_t)n.start + n.len != pool.size()) {  // not at the end of the arena: move
+            const uint32_t at = (uint32_t)pool.size();
+            pool.resize(pool.size() + n.len);
+            if (n.len) memmove(pool.data() + at, pool.data() + n.start, n.len * sizeof(PVal));
+            n.start = at;
+        }
+        pool.push_back(v);
+        ++n.len;
+    }
+    uint8_t *grow_bytes(Node &n, size_t cnt)  // room for cnt more bytes of n; returns where to write them
+    {
+        if ((size_t)n.bstart + n.blen != bytes.size()) {
+            const uint32_t at = (uint32_t)bytes.size();
+            bytes.resize(bytes.size() + n.blen);
+            if (n.blen) memmove(bytes.data() + at, bytes.data() + n.bstart, n.blen);
+            n.bstart = at;
+        }
+        bytes.resize(bytes.size() + cnt);
+        uint8_t *dst = bytes.data() + n.bstart + n.blen;
+        n.blen += (uint32_t)cnt;
+        return dst;
+    }
 };
 
 bool key_is(const PVal &k, const char *name)
@@ -65,35 +96,36 @@ bool key_is(const PVal &k, const char *name)
 const PVal *dict_get(const Graph &g, const PVal &d, const char *name)
 {
     if (d.kind != K_DICT) return nullptr;
-    const std::vector<PVal> &it = g.nodes[d.idx].items;
-    for (size_t i = 0; i + 1 < it.size(); i += 2)
+    const Node &n = g.nodes[d.idx];
+    const PVal *it = g.items(n);
+    for (uint32_t i = 0; i + 1 < n.len; i += 2)
         if (key_is(it[i], name)) return &it[i + 1];
     return nullptr;
 }
 
-void list_append(Node &n, const PVal &v)
+void list_append(Graph &g, Node &n, const PVal &v)
 {
     if (n.all_bytes && v.kind == K_INT && v.i >= 0 && v.i <= 255) {
-        n.bytes.push_back((uint8_t)v.i);
+        *g.grow_bytes(n, 1) = (uint8_t)v.i;
         return;
     }
     if (n.all_bytes) {  // first non-byte element: fall back to generic items
         n.all_bytes = false;
-        n.items.reserve(n.bytes.size() + 1);
-        for (uint8_t b : n.bytes) {
+        for (uint32_t i = 0; i < n.blen; ++i) {
             PVal x;
-            x.kind = K_INT, x.i = b;
-            n.items.push_back(x);
+            x.kind = K_INT, x.i = g.bytes[n.bstart + i];
+            g.push_item(n, x);
         }
-        n.bytes.clear();
+        n.blen = 0;
     }
-    n.items.push_back(v);
+    g.push_item(n, v);
 }
 
 // ---- the virtual machine ------------------------------------------------------------------------------------
 int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
 {
     const uint8_t *p = msg, *end = msg + len;
+    g.nodes.reserve(len / 24 + 16), g.pool.reserve(len / 8 + 16), g.bytes.reserve(len / 2 + 16), g.stack.reserve(1024);
     auto need = [&](size_t n) { return (size_t)(end - p) >= n; };
     auto bad = [&](const char *what) {
         err.set("pickle stream: %s at byte %zu of %zu", what, (size_t)(p - msg), len);
@@ -219,6 +251,20 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
             case '}': g.stack.push_back(new_node(K_DICT)); break;
             case ')': g.stack.push_back(new_node(K_TUPLE)); break;
             case '(': {
+                // fast path: a batch of one-byte integers appended to a byte list, "( K b K b ... e" -- the body of every
+                // Vec<u8> under serde's default representation, i.e. most of the message
+                if (!g.stack.empty() && g.stack.back().kind == K_LIST && g.nodes[g.stack.back().idx].all_bytes &&
+                    g.nodes[g.stack.back().idx].len == 0) {
+                    const uint8_t *q = p;
+                    while (end - q >= 2 && q[0] == 'K') q += 2;
+                    if (q < end && *q == 'e' && q > p) {
+                        const size_t cnt = (size_t)(q - p) / 2;
+                        uint8_t *dst = g.grow_bytes(g.nodes[g.stack.back().idx], cnt);
+                        for (size_t i = 0; i < cnt; ++i) dst[i] = p[2 * i + 1];
+                        p = q + 1;
+                        break;
+                    }
+                }
                 PVal v;
                 v.kind = K_MARK;
                 g.stack.push_back(v);
@@ -229,14 +275,14 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
                 const PVal v = g.stack.back();
                 g.stack.pop_back();
                 if (v.kind == K_MARK) return bad("APPEND of a mark");
-                list_append(g.nodes[g.stack.back().idx], v);
+                list_append(g, g.nodes[g.stack.back().idx], v);
                 break;
             }
             case 'e': {  // APPENDS
                 size_t m;
                 if (!find_mark(m) || m == 0 || g.stack[m - 1].kind != K_LIST) return bad("APPENDS without mark / list");
                 Node &n = g.nodes[g.stack[m - 1].idx];
-                for (size_t i = m + 1; i < g.stack.size(); ++i) list_append(n, g.stack[i]);
+                for (size_t i = m + 1; i < g.stack.size(); ++i) list_append(g, n, g.stack[i]);
                 g.stack.resize(m);
                 break;
             }
@@ -246,7 +292,7 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
                 if (v.kind == K_MARK || k.kind == K_MARK) return bad("SETITEM of a mark");
                 g.stack.resize(g.stack.size() - 2);
                 Node &n = g.nodes[g.stack.back().idx];
-                n.items.push_back(k), n.items.push_back(v);
+                g.push_item(n, k), g.push_item(n, v);
                 break;
             }
             case 'u': {  // SETITEMS
@@ -254,7 +300,7 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
                 if (!find_mark(m) || m == 0 || g.stack[m - 1].kind != K_DICT || ((g.stack.size() - m - 1) & 1))
                     return bad("SETITEMS without mark / dict / pairs");
                 Node &n = g.nodes[g.stack[m - 1].idx];
-                n.items.insert(n.items.end(), g.stack.begin() + m + 1, g.stack.end());
+                for (size_t i = m + 1; i < g.stack.size(); ++i) g.push_item(n, g.stack[i]);
                 g.stack.resize(m);
                 break;
             }
@@ -267,9 +313,9 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
                 PVal c = new_node(op == 't' ? K_TUPLE : op == 'l' ? K_LIST : K_DICT);
                 Node &n = g.nodes[c.idx];
                 if (op == 'l')
-                    for (size_t i = m + 1; i < g.stack.size(); ++i) list_append(n, g.stack[i]);
+                    for (size_t i = m + 1; i < g.stack.size(); ++i) list_append(g, n, g.stack[i]);
                 else
-                    n.items.assign(g.stack.begin() + m + 1, g.stack.end());
+                    for (size_t i = m + 1; i < g.stack.size(); ++i) g.push_item(n, g.stack[i]);
                 g.stack.resize(m);
                 g.stack.push_back(c);
                 break;
@@ -282,7 +328,7 @@ int32_t run_vm(const uint8_t *msg, size_t len, Graph &g, ErrBuf &err)
                 for (size_t i = g.stack.size() - k; i < g.stack.size(); ++i)
                     if (g.stack[i].kind == K_MARK) return bad("TUPLEn over a mark");
                 PVal c = new_node(K_TUPLE);
-                g.nodes[c.idx].items.assign(g.stack.end() - k, g.stack.end());
+                for (size_t i = g.stack.size() - k; i < g.stack.size(); ++i) g.push_item(g.nodes[c.idx], g.stack[i]);
                 g.stack.resize(g.stack.size() - k);
                 g.stack.push_back(c);
                 break;
@@ -335,7 +381,7 @@ int32_t tensor_blob(const Graph &g, const PVal &t, BlobView &b, const char *what
         return RRL_EFORMAT;
     }
     if (d->kind == K_BYTES) return parse_blob(d->s.p, d->s.n, b, err);
-    if (d->kind == K_LIST && g.nodes[d->idx].all_bytes) return parse_blob(g.nodes[d->idx].bytes.data(), g.nodes[d->idx].bytes.size(), b, err);
+    if (d->kind == K_LIST && g.nodes[d->idx].all_bytes) return parse_blob(g.byte_data(g.nodes[d->idx]), g.nodes[d->idx].blen, b, err);
     err.set("action %lld: %s.data is neither bytes nor a list of byte values", (long long)r, what);
     return RRL_EFORMAT;
 }
@@ -351,10 +397,10 @@ bool number(const PVal &v, float &out)
 int32_t data_value(const Graph &g, const PVal &v, float &out, const char *what, int64_t r, ErrBuf &err)
 {
     const PVal *payload = &v;
-    if (v.kind == K_DICT && g.nodes[v.idx].items.size() == 2 && !dict_get(g, v, "data"))
-        payload = &g.nodes[v.idx].items[1];
-    else if (v.kind == K_TUPLE && g.nodes[v.idx].items.size() == 2 && g.nodes[v.idx].items[0].kind == K_STR)
-        payload = &g.nodes[v.idx].items[1];
+    if (v.kind == K_DICT && g.nodes[v.idx].len == 2 && !dict_get(g, v, "data"))
+        payload = g.items(g.nodes[v.idx]) + 1;
+    else if (v.kind == K_TUPLE && g.nodes[v.idx].len == 2 && g.items(g.nodes[v.idx])[0].kind == K_STR)
+        payload = g.items(g.nodes[v.idx]) + 1;
     if (number(*payload, out)) return RRL_OK;
     if (payload->kind == K_DICT) {
         BlobView b;
@@ -423,13 +469,14 @@ int32_t action_row(const Graph &g, const PVal &a, int64_t r, int d, int A, bool 
 }
 
 // the message's top object: the Vec<RelayRLAction> itself (a list; a tuple is tolerated)
-int32_t top_actions(const Graph &g, const std::vector<PVal> *&items, ErrBuf &err)
+int32_t top_actions(const Graph &g, const PVal *&items, int64_t &n, ErrBuf &err)
 {
-    if ((g.top.kind != K_LIST && g.top.kind != K_TUPLE) || (g.top.kind == K_LIST && !g.nodes[g.top.idx].bytes.empty())) {
+    if ((g.top.kind != K_LIST && g.top.kind != K_TUPLE) || (g.top.kind == K_LIST && g.nodes[g.top.idx].blen != 0)) {
         err.set("pickle message is not a sequence of actions (Vec<RelayRLAction>, src/types/trajectory.rs:50-55)");
         return RRL_EFORMAT;
     }
-    items = &g.nodes[g.top.idx].items;
+    items = g.items(g.nodes[g.top.idx]);
+    n = g.nodes[g.top.idx].len;
     return RRL_OK;
 }
 
@@ -451,14 +498,14 @@ extern "C" int32_t rrl_decode_pickle_trajectory(const uint8_t *msg, size_t len, 
         Graph g;
         *count = 0;
         RRL_TRY(run_vm(msg, len, g, err));
-        const std::vector<PVal> *items = nullptr;
-        RRL_TRY(top_actions(g, items, err));
-        const int64_t n = (int64_t)items->size();
+        const PVal *items = nullptr;
+        int64_t n = 0;
+        RRL_TRY(top_actions(g, items, n, err));
         if (n > cap) {
             err.set("trajectory holds %lld actions, more than the %lld rows the caller provided", (long long)n, (long long)cap);
             return RRL_ECAPACITY;
         }
-        for (int64_t r = 0; r < n; ++r) RRL_TRY(action_row(g, (*items)[(size_t)r], r, obs_dim, act_dim, with_baseline != 0, o, err));
+        for (int64_t r = 0; r < n; ++r) RRL_TRY(action_row(g, items[r], r, obs_dim, act_dim, with_baseline != 0, o, err));
         *count = n;
         return RRL_OK;
     });
@@ -476,9 +523,9 @@ extern "C" int32_t rrl_ingest_pickle(rrl_learner_t *h, const uint8_t *msg, size_
         const int d = h->cfg.obs_dim, A = h->cfg.act_dim;
         Graph g;
         RRL_TRY(run_vm(msg, len, g, h->err));
-        const std::vector<PVal> *items = nullptr;
-        RRL_TRY(top_actions(g, items, h->err));
-        const int64_t n = (int64_t)items->size();
+        const PVal *items = nullptr;
+        int64_t n = 0;
+        RRL_TRY(top_actions(g, items, n, h->err));
         if (n_actions) *n_actions = n;
         if (n == 0) return RRL_OK;
         // rows in chunks, all of the message or none of it (see rrl_ingest_grpc_trajectory)
@@ -489,7 +536,7 @@ extern "C" int32_t rrl_ingest_pickle(rrl_learner_t *h, const uint8_t *msg, size_
             const int64_t hi = std::min<int64_t>(n, lo + INGEST_CHUNK_ROWS);
             int32_t st = RRL_OK;
             for (int64_t r = lo; r < hi && st == RRL_OK; ++r) {
-                st = action_row(g, (*items)[(size_t)r], r - lo, d, A, h->cfg.with_baseline != 0, cols.view, h->err);
+                st = action_row(g, items[r], r - lo, d, A, h->cfg.with_baseline != 0, cols.view, h->err);
                 if (st != RRL_OK && lo > 0) {  // row numbers in messages count from the start of the trajectory
                     const std::string m = h->err.msg;
                     h->err.set("(chunk starting at action %lld) %s", (long long)lo, m.c_str());
