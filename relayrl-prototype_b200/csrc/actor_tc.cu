@@ -101,8 +101,8 @@ constexpr int OFF_BIAS = OFF_W3V + 4 * 256 * 4;                       // f32 b1 
 constexpr int OFF_B3 = OFF_BIAS + 4 * 256 * 4;                        // f32 [32] policy + [1] value (+ pad)
 constexpr int OFF_COMB = OFF_B3 + 256;                                // f32 [128][33]: the two column halves meet here
 constexpr int OFF_VCOMB = OFF_COMB + AT_M * (AT_MAX_A + 1) * 4;       // f32 [128]
-constexpr int OFF_BAR = OFF_VCOMB + AT_M * 4;                         // mbarriers: full[6] empty[6] acc_full acc_empty a_ready
-constexpr int AT_SMEM_BYTES = OFF_BAR + (2 * AT_STAGES + 3) * 8 + 8;
+constexpr int OFF_BAR = OFF_VCOMB + AT_M * 4;                         // mbarriers: full[6] empty[6] acc_full acc_empty a_ready planes_ready
+constexpr int AT_SMEM_BYTES = OFF_BAR + (2 * AT_STAGES + 4) * 8 + 8;
 static_assert(AT_SMEM_BYTES <= 227 * 1024, "tensor-core actor kernel exceeds shared memory");
 static_assert(OFF_RING % 128 == 0 && OFF_BAR % 8 == 0, "alignment");
 
@@ -127,8 +127,8 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
     float *bias_s = reinterpret_cast<float *>(smem + OFF_BIAS), *b3_s = reinterpret_cast<float *>(smem + OFF_B3);
     float *comb_s = reinterpret_cast<float *>(smem + OFF_COMB), *vcomb_s = reinterpret_cast<float *>(smem + OFF_VCOMB);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + OFF_BAR), *empty = full + AT_STAGES;
-    uint64_t *acc_full = empty + AT_STAGES, *acc_empty = acc_full + 1, *a_ready = acc_full + 2;
-    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(a_ready + 1);
+    uint64_t *acc_full = empty + AT_STAGES, *acc_empty = acc_full + 1, *a_ready = acc_full + 2, *planes_ready = acc_full + 3;
+    uint32_t *tmem_s = reinterpret_cast<uint32_t *>(planes_ready + 1);
 
     constexpr int NC = H / AT_NCHUNK;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         mbar_init(acc_full, 1);
         mbar_init(acc_empty, AT_WORKERS / 32);
         mbar_init(a_ready, AT_WORKERS / 32);
+        mbar_init(planes_ready, AT_WORKERS / 32);
         mbar_fence_init();
     }
     fence_before_sync();
@@ -183,14 +184,20 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         // Descriptors are built once per ring block (one move into uniform registers) and stepped by compile-time constants:
         // with a descriptor computed per MMA the issue loop ran at 161 cycles per MMA instead of the tensor core's 64.
         constexpr uint64_t SUBQ = AT_SUB >> 4, PLQ = OBS_PLANE >> 4;
-        uint32_t st = 0, ph = 0, chunk_n = 0, tcount = 0;
+        uint32_t st = 0, ph = 0, chunk_n = 0, tcount = 0, net_n = 0;
         auto next_stage = [&]() {
             if (++st == AT_STAGES) st = 0, ph ^= 1u;
         };
-        auto run_chunk = [&](auto l1_tag, int ks) {
+        // wait_at: the K step of layer 2 before which the planes written by the LAST epilogue of layer 1 must be complete (the
+        // earlier K steps read planes of earlier chunks, so layer 2 starts while that epilogue is still splitting its values)
+        auto run_chunk = [&](auto l1_tag, int ks, int wait_at, uint32_t wait_parity) {
             constexpr bool L1 = decltype(l1_tag)::value;
             const uint32_t acc_t = tmem + AT_TM_ACC;
             for (int s = 0; s < ks; ++s) {  // cross pass: the five small products of K step s
+                if (s == wait_at) {
+                    mbar_wait(planes_ready, wait_parity);
+                    fence_after_sync();
+                }
                 AT_WAIT_FULL(&full[st], ph);
                 const uint64_t bd = smem_desc(ring_u + st * AT_BLOCK, 2048, 128);
                 if (L1) {
@@ -229,15 +236,15 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++tcount) {
             mbar_wait(a_ready, tcount & 1u);  // this tile's observation planes are in shared memory
             fence_after_sync();
-            for (int net = 0; net < nets; ++net)
+            for (int net = 0; net < nets; ++net, ++net_n)
                 for (int layer = 1; layer <= 2; ++layer)
                     for (int c = 0; c < NC; ++c, ++chunk_n) {
                         mbar_wait(acc_empty, (chunk_n & 1u) ^ 1u);  // the epilogue has read the previous chunk
                         fence_after_sync();
                         if (layer == 1)
-                            run_chunk(std::true_type{}, ps.ks1);
+                            run_chunk(std::true_type{}, ps.ks1, -1, 0u);
                         else
-                            run_chunk(std::false_type{}, H / 16);
+                            run_chunk(std::false_type{}, H / 16, c == 0 ? (NC - 1) * (AT_NCHUNK / 16) : -1, net_n & 1u);
                         mma_commit_warp(acc_full);
                     }
         }
@@ -312,7 +319,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     float v[64];
                     load_chunk(v, b1, c);
                     const bool last = c + 1 == NC;
-                    if (!last) arrive(acc_empty);  // the next chunk of layer 1 may overwrite the accumulator already
+                    arrive(acc_empty);  // the values are in registers: the next chunk (layer 1, or the first K steps of layer 2) may start
 #ifndef AT_DBG_NO_EPI
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -330,7 +337,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1) actor_tc_kernel(ActorArgs a)
                     if (v[3] == 123.f) vcomb_s[row] = v[5];
 #endif
                     if (last) {
-                        arrive(acc_empty);  // layer 2 reads the planes: only now
+                        arrive(planes_ready);  // layer 2 may now read the planes of this chunk's units too
                         // every MMA that reads the observation planes has retired: the next tile's can be built under layer 2
                         if (net == nets - 1 && tile + gridDim.x < tiles) convert_obs(tile + gridDim.x);
                     }
