@@ -495,9 +495,11 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 const float tot = reduce_scatter16(p, lane);  // row 16*rq + (lane & 15), summed over this warp's 32 units
                 if (lane < TC_RPT) vpart_s[(q * TC_MAX_OUT + o_) * TILE_M + TC_RPT * rq + lane] = tot;
             }
+            TCT(12);
             fence_before_sync();
             worker_sync();  // (also: every warp has read D1[k & 1])
             fence_after_sync();
+            TCT(13);
             // H1^T of this tile -> tensor memory (G3's A operand): recomputed exactly as stage 1 did; planes 0 and 1 go where
             // D1[k & 1] was, plane 2 has its own 32 columns
             {
@@ -509,6 +511,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 tmem_st8(tmem_lane + TM_P2 + (TC_RPT / 2) * rq, hk[2]);
                 hb_carry = hbits;  // the relu mask epilogue 2 needs one tile later: same thread, stays in a register
             }
+            TCT(14);
             // per-row loss and dhead: lane l of every warp works out row 16*rq + (l & 15); the four unit
             // quarters do it redundantly (it is a handful of instructions), only q == 0 keeps the sums
             float g_lane;
@@ -563,6 +566,7 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                         for (int o_ = 0; o_ < TC_MAX_OUT; ++o_) db3acc[o_] += (o_ == at_lane) ? g_lane : 0.f;
                 }
             }
+            TCT(15);
             // dz2 = dhead W3 [h2 > 0] -> transposed planes (two 16-byte pieces of 8 rows per plane); dW3, db2
             float dbl = 0.f;
             const float w3j = w3_s[j];

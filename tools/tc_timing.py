@@ -16,8 +16,8 @@ torch.cuda.synchronize()
 f(out, 0)
 v = list(out)
 print("variant", VAR)
-names = ["mma:wait go23", "mma:G3 issue", "mma:G2 issue", "mma:wait go1", "mma:G1 issue", "wrk:wait bar1", "wrk:epi1+H1T->go23", "wrk:wait bar3+drain", "wrk:stage1(next)", "wrk:(unused)", "wrk:wait bar2+epi2", "wrk:spill"]
-m = sum(v[:5]); w = sum(v[5:12])
+names = ["mma:wait go23", "mma:G3 issue", "mma:G2 issue", "mma:wait go1", "mma:G1 issue", "wrk:wait bar1", "wrk:e1 dz2+wait G2+go23", "wrk:wait bar3+drain", "wrk:stage1(next)", "wrk:(unused)", "wrk:epi2 math", "wrk:spill", "wrk:e1 D1+head reduce", "wrk:e1 barrier", "wrk:e1 H1T->TMEM", "wrk:e1 row loss"]
+m = sum(v[:5]); w = sum(v[5:16])
 TILES = 2 * 81 * 111   # launches of the bench run (2 epochs x 81 passes) x tiles of CTA 0 at 1 Mi transitions (approx.)
 for i, (n, x) in enumerate(zip(names, v)):
     tot = m if i < 5 else w
