@@ -357,11 +357,12 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
             float v[16], s[16];
-            tmem_ld16(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v);
-            if (!first_in_window) {
-                tmem_ld16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, s);
+            if (!first_in_window) {  // (warp-uniform) both loads in flight, one wait
+                tmem_ld16x2(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v, tmem_lane + TM_ACC + 32 * rq + 16 * hf, s);
 #pragma unroll
                 for (int c = 0; c < 16; ++c) v[c] += s[c];
+            } else {
+                tmem_ld16(tmem_lane + TM_DW2 + 32 * rq + 16 * hf, v);
             }
             tmem_st16(tmem_lane + TM_ACC + 32 * rq + 16 * hf, v);
         }
@@ -506,9 +507,10 @@ __global__ void __launch_bounds__(TC_CTA_THREADS, 1) mlp_tc_kernel(MlpArgs a)
                 uint32_t hk[3][TC_RPT / 2], hbits;
                 h1_words(b3, hk, hbits);
                 const uint32_t hT = tmem_lane + TM_D1 + 64 * (k & 1) + (TC_RPT / 2) * rq;
-                tmem_st8(hT, hk[0]);
-                tmem_st8(hT + 32, hk[1]);
-                tmem_st8(tmem_lane + TM_P2 + (TC_RPT / 2) * rq, hk[2]);
+                tmem_st8_nowait(hT, hk[0]);
+                tmem_st8_nowait(hT + 32, hk[1]);
+                tmem_st8_nowait(tmem_lane + TM_P2 + (TC_RPT / 2) * rq, hk[2]);
+                tmem_st_wait();
                 hb_carry = hbits;  // the relu mask epilogue 2 needs one tile later: same thread, stays in a register
             }
             TCT(14);
