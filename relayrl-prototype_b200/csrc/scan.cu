@@ -282,7 +282,9 @@ __device__ __forceinline__ void scan_prepare(const ScanArgs &a, TileBuf &B, int6
         __syncwarp();
     }
     SCT(9, lane == 0);  // producer: search + mask
+#ifndef SCAN_DBG_NO_WAIT  // (timing experiment only, wrong results: is the producer's wait for its data exposed?  measured: no)
     asm volatile("cp.async.wait_all;" ::: "memory");
+#endif
     SCT(10, lane == 0);  // producer: wait for the data
 }
 
