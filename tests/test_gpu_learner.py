@@ -259,6 +259,9 @@ def test_plugin_class_end_to_end(tmp_path):
     assert m.get_input_dim() == 4 and m.get_output_dim() == 2
     act, data = m.step(torch.zeros(1, 4), torch.zeros(1, 2))
     assert isinstance(act, torch.Tensor) and len(data) > 0 and "logp_a" in data and "v" in data
+    assert tuple(data["logp_a"].shape) == (1, 1)               # [1, d] in: the reference's unsqueeze of a [1, 1] action
+    act1, data1 = m.step(torch.zeros(4), torch.zeros(2))       # the 1-D observation agents send (o3_action.rs:256-265)
+    assert tuple(act1.shape) == (1,) and tuple(data1["logp_a"].shape) == (1,)   # as kernel.py:33-37 returns it
     sd = m.state_dict()
     np.testing.assert_allclose(sd["policy.pi_network.2.weight"].numpy().reshape(-1),
                                algo.learner.get_params(0)[4 * 128 + 128:4 * 128 + 128 + 128 * 128], rtol=0, atol=0)
